@@ -1,0 +1,70 @@
+"""ctypes binding of the C ABI (include/houv_b200.h).  No CPU fallback: if the
+library is missing it is built with nvcc, and if that fails the import of any
+operator raises."""
+import ctypes
+import os
+
+from . import build as _build
+
+_LIB = None
+
+_vp = ctypes.c_void_p
+_ci = ctypes.c_int
+
+# name -> argtypes; every entry point returns int (0 = ok) unless noted
+_SIGNATURES = {
+    "houv_chamfer3d_forward": [_vp, _vp, _ci, _ci, _ci, _vp, _vp, _vp, _vp, _vp],
+    "houv_nn_search": [_vp, _vp, _ci, _ci, _ci, _vp, _vp, _vp],
+    "houv_chamfer3d_backward": [_vp, _vp, _vp, _vp, _vp, _vp, _ci, _ci, _ci, _vp, _vp, _vp],
+    "houv_set_nn_variant": [_ci],
+    "houv_fp32_probe": [_vp, _ci, _ci, ctypes.POINTER(ctypes.c_double), _vp],
+}
+
+EXPORTS = tuple(_SIGNATURES) + ("houv_version",)
+
+
+def lib_path():
+    return _build.LIB
+
+
+def load():
+    """Load (building first if needed) libhouv_b200.so."""
+    global _LIB
+    if _LIB is None:
+        path = _build.build()
+        lib = ctypes.CDLL(path)
+        for name, args in _SIGNATURES.items():
+            fn = getattr(lib, name)
+            fn.argtypes = args
+            fn.restype = _ci
+        lib.houv_version.restype = ctypes.c_char_p
+        lib.houv_version.argtypes = []
+        _LIB = lib
+    return _LIB
+
+
+class HouvError(RuntimeError):
+    pass
+
+
+def check(code, what):
+    if code != 0:
+        raise HouvError("%s failed with code %d" % (what, code))
+
+
+def stream_ptr():
+    """cudaStream_t of torch's current stream as an integer handle."""
+    import torch
+    return torch.cuda.current_stream().cuda_stream
+
+
+def require_cuda_f32(t, name, last=None):
+    """The reference surfaces dtype/device mismatches as c10::Error from
+    .data<float>() (chamfer_cuda.cpp:17-27); we raise RuntimeError up front."""
+    import torch
+    if not isinstance(t, torch.Tensor) or not t.is_cuda:
+        raise RuntimeError("%s must be a CUDA tensor (houv_b200 has no CPU path)" % name)
+    if t.dtype != torch.float32:
+        raise RuntimeError("%s must be float32, got %s" % (name, t.dtype))
+    if last is not None and (t.dim() != 3 or t.shape[-1] != last):
+        raise RuntimeError("%s must be [B, points, %d], got %s" % (name, last, tuple(t.shape)))

@@ -1,0 +1,45 @@
+// Shared device helpers for the houv_b200 kernels (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/houv_b200.h"
+
+#if defined(__CUDA_ARCH__) && (__CUDA_ARCH__ < 1000)
+#error "houv_b200 is written for sm_100a (B200) only"
+#endif
+
+namespace houv {
+
+// 3-input minimum (SASS FMNMX3, one ALU-pipe slot for two candidates).
+// IEEE minNum semantics: a NaN operand is ignored, as `d < best` ignores it in
+// the reference (chamfer3D.cu:46).
+__device__ __forceinline__ float min3(float a, float b, float c) {
+    float r;
+    asm("min.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c));
+    return r;
+}
+
+// The reference's squared distance with nvcc's contraction spelled out
+// (chamfer3D.cu:32-35 -> FADD,FADD,FADD,FMUL(y),FFMA(x),FFMA(z)); the _rn
+// intrinsics are never re-contracted by the compiler.
+__device__ __forceinline__ float sqdist_ref(float tx, float ty, float tz, float qx, float qy,
+                                            float qz) {
+    float dx = __fsub_rn(tx, qx), dy = __fsub_rn(ty, qy), dz = __fsub_rn(tz, qz);
+    return __fmaf_rn(dz, dz, __fmaf_rn(dx, dx, __fmul_rn(dy, dy)));
+}
+
+// Two evaluations per issue slot (FADD2/FMUL2/FFMA2). nq* hold the NEGATED
+// query coordinate in both halves: t + (-q) == t - q bit for bit.
+__device__ __forceinline__ float2 sqdist2(float2 tx, float2 ty, float2 tz, float2 nqx, float2 nqy,
+                                          float2 nqz) {
+    float2 dx = __fadd2_rn(tx, nqx), dy = __fadd2_rn(ty, nqy), dz = __fadd2_rn(tz, nqz);
+    return __ffma2_rn(dz, dz, __ffma2_rn(dx, dx, __fmul2_rn(dy, dy)));
+}
+
+inline int check_launch() {
+    cudaError_t e = cudaGetLastError();
+    return e == cudaSuccess ? 0 : (int)e;
+}
+
+}  // namespace houv

@@ -1,0 +1,75 @@
+/* houv_b200 -- C ABI of the B200-native (sm_100a) HOUV registration hot path.
+ *
+ * This is the drop-in boundary: plain pointers and sizes, no torch types.
+ * Every pointer is a DEVICE pointer unless its name ends in _host.  All
+ * buffers are caller-owned; the library never allocates or frees behind the
+ * caller's back and keeps no global state besides the tuning knobs.
+ * `stream` is a cudaStream_t passed as void* (NULL = legacy default stream);
+ * every call only ENQUEUES work on it and is CUDA-graph capturable.
+ * Return value: 0 = ok, otherwise a cudaError_t (or HOUV_E_* below) --
+ * the reference's pybind entry points return 1/0 and printf
+ * (chamfer3D.cu:145-151, 187-193); the Python binding maps our codes to
+ * RuntimeError.
+ *
+ * Reference interfaces replaced (paths relative to /root/reference):
+ *   houv_chamfer3d_forward   <- chamfer_3D.forward  utils/metrics/CD/chamfer3D/chamfer_cuda.cpp:17-19,31
+ *                               = chamfer_cuda_forward            chamfer3D.cu:136-154
+ *   houv_chamfer3d_backward  <- chamfer_3D.backward chamfer_cuda.cpp:22-27,32
+ *                               = chamfer_cuda_backward           chamfer3D.cu:176-195
+ *   houv_nn_search           <- one NmDistanceKernel launch       chamfer3D.cu:12-134,142
+ *   houv_kabsch              <- SVDHead.forward     registration/model_utils.py:220-255
+ *   houv_icp                 <- o3d registration_icp call site    registration/train_ICP.py:148-151
+ *   houv_pose_optimise       <- predict_model hot loop            registration/models/houv.py:106-138
+ */
+#ifndef HOUV_B200_H
+#define HOUV_B200_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define HOUV_E_BADARG 100001 /* null pointer / negative size */
+#define HOUV_E_TOOBIG 100002 /* B*N*3 or B*M*3 would overflow the index math */
+
+/* Library identification, e.g. "houv_b200 0.1 sm_100a". */
+const char *houv_version(void);
+
+/* Bidirectional Chamfer NN search.
+ *   xyz1[B,N,3], xyz2[B,M,3] float32 row-major (AoS xyz)
+ *   dist1[B,N] = min_j |xyz1_i - xyz2_j|^2, idx1[B,N] = FIRST arg-min j (int32)
+ *   dist2[B,M], idx2[B,M] likewise with the roles swapped.
+ * Arithmetic is the reference's, bit for bit: d = fma(dz,dz,fma(dx,dx,dy*dy)),
+ * dx = target.x - query.x, strict '<' in ascending j  (chamfer3D.cu:32-36,126).
+ * Outputs need not be pre-zeroed.  M == 0 (or N == 0) zero-fills the affected
+ * outputs, which is what the reference's zero-initialised buffers end up as. */
+int houv_chamfer3d_forward(const float *xyz1, const float *xyz2, int B, int N, int M,
+                           float *dist1, float *dist2, int *idx1, int *idx2, void *stream);
+
+/* One directed search: query[B,N,3] against target[B,M,3] -> dist[B,N], idx[B,N]. */
+int houv_nn_search(const float *query, const float *target, int B, int N, int M,
+                   float *dist, int *idx, void *stream);
+
+/* Gradient scatter of both directions, fused in one launch.
+ *   g = 2*graddist1[b,i];  gradxyz1[b,i]      += g*(xyz1[b,i]-xyz2[b,idx1[b,i]])
+ *                          gradxyz2[b,idx1..] -= the same            (chamfer3D.cu:155-174)
+ *   and symmetrically for graddist2/idx2.
+ * gradxyz1/gradxyz2 are ACCUMULATED INTO (float atomics, like the reference) and
+ * must arrive zero-filled for a plain backward (dist_chamfer_3D.py:56-60). */
+int houv_chamfer3d_backward(const float *xyz1, const float *xyz2, const float *graddist1,
+                            const float *graddist2, const int *idx1, const int *idx2, int B,
+                            int N, int M, float *gradxyz1, float *gradxyz2, void *stream);
+
+/* Tuning knob for the NN kernel shape: variant 0..3 = (queries/thread, threads/CTA)
+ * (2,128) (4,128) (4,64) (2,256); -1 = built-in default.  Returns the old value. */
+int houv_set_nn_variant(int variant);
+
+/* FP32 CUDA-core peak probe: runs `iters` x 64 dependent-free FFMA per thread on a
+ * full-chip grid; *flop_host receives the FLOP it executed (2 per FFMA lane-op).
+ * Time it with events around the call to get the roofline denominator. */
+int houv_fp32_probe(float *scratch /* >= 4 floats */, int iters, int packed,
+                    double *flop_host, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* HOUV_B200_H */

@@ -1,0 +1,96 @@
+"""Generates the committed golden fixtures.  Runs ONLY in the dev container,
+where /root/reference exists; the GPU box consumes the .npz files.
+
+    python tests/golden/make_golden.py            # all fixtures
+    python tests/golden/make_golden.py chamfer    # one family
+
+chamfer_unit.npz
+    the reference's own unit test case (utils/metrics/CD/unit_test.py:14-33:
+    rand(4,100,3) vs rand(4,200,3)) with
+      py_*   = outputs of the reference's chamfer_python.distChamfer, imported
+               as-is from /root/reference/utils/metrics/CD/chamfer_python.py
+      ref_*  = outputs of the reference's CUDA kernel SOURCE compiled for the
+               host (oracle/_ref/libref_chamfer.so, see oracle/Makefile)
+chamfer_cases.npz
+    ragged / tie / tile-boundary cases, ref_* outputs as above.
+"""
+import os
+import sys
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+sys.path.insert(0, ROOT)
+REF = "/root/reference"
+
+
+def chamfer_cases():
+    """name -> (xyz1, xyz2); shared with the tests through the fixture file."""
+    rng = np.random.RandomState(1234)
+    f32 = np.float32
+    cases = {}
+    cases["ragged_7x13"] = (rng.rand(3, 7, 3), rng.rand(3, 13, 3))
+    cases["one_target"] = (rng.rand(2, 33, 3), rng.rand(2, 1, 3))
+    cases["tile_edge_511_513"] = (rng.rand(2, 511, 3), rng.rand(2, 513, 3))
+    cases["odd_1000_1537"] = (rng.rand(2, 1000, 3), rng.rand(2, 1537, 3))
+    # exact ties: duplicated targets (first index must win), also across the
+    # 512-tile boundary of the reference and the 8-wide groups of our kernel
+    t = rng.rand(1, 600, 3)
+    t[0, 300] = t[0, 5]
+    t[0, 517] = t[0, 5]
+    t[0, 599] = t[0, 510]
+    q = np.concatenate([t[:, [5, 510, 7]] + 1e-3, rng.rand(1, 40, 3)], axis=1)
+    cases["dup_targets"] = (q, t)
+    # grid-quantised coordinates: many exactly equal distances
+    cases["grid_ties"] = (rng.randint(0, 4, (2, 200, 3)) / 4.0, rng.randint(0, 4, (2, 300, 3)) / 4.0)
+    # identical clouds: d == 0 everywhere, idx == own index unless duplicated
+    same = rng.rand(1, 257, 3)
+    cases["identical"] = (same, same.copy())
+    # negative / larger-magnitude coordinates (MVP clouds are centred)
+    cases["centred"] = (rng.randn(2, 300, 3) * 0.3, rng.randn(2, 260, 3) * 0.3)
+    return {k: (a.astype(f32), b.astype(f32)) for k, (a, b) in cases.items()}
+
+
+def make_chamfer():
+    import torch
+    from oracle import chamfer as oc
+    sys.path.insert(0, os.path.join(REF, "utils/metrics/CD"))
+    import chamfer_python  # the reference's own file, unmodified
+
+    torch.manual_seed(0)
+    p1 = torch.rand(4, 100, 3)
+    p2 = torch.rand(4, 200, 3)
+    py = chamfer_python.distChamfer(p1, p2)
+    x1, x2 = p1.numpy(), p2.numpy()
+    ref = oc.ref_chamfer_forward(x1, x2)
+    rng = np.random.RandomState(7)
+    gd1 = rng.randn(4, 100).astype(np.float32)
+    gd2 = rng.randn(4, 200).astype(np.float32)
+    g1, g2 = oc.ref_chamfer_backward(x1, x2, gd1, gd2, ref[2], ref[3])
+    np.savez_compressed(
+        os.path.join(HERE, "chamfer_unit.npz"), xyz1=x1, xyz2=x2,
+        py_dist1=py[0].numpy(), py_dist2=py[1].numpy(), py_idx1=py[2].numpy(),
+        py_idx2=py[3].numpy(), ref_dist1=ref[0], ref_dist2=ref[1], ref_idx1=ref[2],
+        ref_idx2=ref[3], graddist1=gd1, graddist2=gd2, ref_gradxyz1=g1, ref_gradxyz2=g2)
+
+    out = {}
+    for name, (a, b) in chamfer_cases().items():
+        d1, d2, i1, i2 = oc.ref_chamfer_forward(a, b)
+        rs = np.random.RandomState(len(name))
+        gd1 = rs.randn(*d1.shape).astype(np.float32)
+        gd2 = rs.randn(*d2.shape).astype(np.float32)
+        g1, g2 = oc.ref_chamfer_backward(a, b, gd1, gd2, i1, i2)
+        for k, v in dict(xyz1=a, xyz2=b, dist1=d1, dist2=d2, idx1=i1, idx2=i2, gd1=gd1, gd2=gd2,
+                         g1=g1, g2=g2).items():
+            out[name + "/" + k] = v
+    np.savez_compressed(os.path.join(HERE, "chamfer_cases.npz"), **out)
+    print("chamfer fixtures written")
+
+
+FAMILIES = {"chamfer": make_chamfer}
+
+if __name__ == "__main__":
+    want = sys.argv[1:] or list(FAMILIES)
+    for w in want:
+        FAMILIES[w]()

@@ -1,0 +1,90 @@
+"""Kernel micro-benchmarks on one B200 (CUDA events, warm-up, L2 flush between
+iterations).  Not the contract bench (that is bench.py); this is the tuning tool.
+
+    python tools/microbench.py probe            # FP32 FFMA peak (scalar and packed)
+    python tools/microbench.py chamfer          # K1/K2 at BASELINE configs C2 and C5
+"""
+import ctypes
+import json
+import os
+import sys
+
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from houv_b200 import _lib  # noqa: E402
+
+
+def timeit(fn, iters=20, warmup=5, flush=None):
+    for _ in range(warmup):
+        fn()
+    torch.cuda.synchronize()
+    ts = []
+    for _ in range(iters):
+        if flush is not None:
+            flush.add_(1.0)  # 256 MB write: evicts the 126 MB L2
+        s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s.record()
+        fn()
+        e.record()
+        torch.cuda.synchronize()
+        ts.append(s.elapsed_time(e))
+    ts.sort()
+    return ts[len(ts) // 2], ts[0]
+
+
+def fp32_peak(packed, iters=4096):
+    lib = _lib.load()
+    scratch = torch.zeros(16, device="cuda")
+    flop = ctypes.c_double(0)
+
+    def run():
+        _lib.check(lib.houv_fp32_probe(scratch.data_ptr(), iters, int(packed), ctypes.byref(flop),
+                                       _lib.stream_ptr()), "probe")
+    med, best = timeit(run, iters=10, warmup=3)
+    return {"packed": bool(packed), "tflops_median": flop.value / med / 1e9,
+            "tflops_best": flop.value / best / 1e9, "ms": med}
+
+
+def cmd_probe():
+    for p in (0, 1):
+        print(json.dumps(fp32_peak(p)))
+
+
+def cmd_chamfer():
+    from houv_b200.chamfer import chamfer_3DDist, chamfer_3D
+    lib = _lib.load()
+    flush = torch.zeros(64 * 1024 * 1024, device="cuda")
+    peak = fp32_peak(0)["tflops_best"]
+    print(json.dumps({"fp32_peak_tflops": peak}))
+    for name, (B, N, M) in {"C2": (32, 2048, 2048), "C5": (64, 16384, 2048),
+                            "unit_timing": (32, 2000, 1000), "B1": (1, 2048, 2048),
+                            "rows6400": (6400, 2048, 2048)}.items():
+        torch.manual_seed(0)
+        x1 = torch.rand(B, N, 3, device="cuda")
+        x2 = torch.rand(B, M, 3, device="cuda")
+        d1 = torch.empty(B, N, device="cuda")
+        d2 = torch.empty(B, M, device="cuda")
+        i1 = torch.empty(B, N, device="cuda", dtype=torch.int32)
+        i2 = torch.empty(B, M, device="cuda", dtype=torch.int32)
+        for variant in (0, 1, 2, 3):
+            lib.houv_set_nn_variant(variant)
+            med, best = timeit(lambda: chamfer_3D.forward(x1, x2, d1, d2, i1, i2), flush=flush)
+            evals = 2.0 * B * N * M
+            print(json.dumps({"case": name, "kernel": "K1 fwd", "variant": variant,
+                              "ms_median": round(med, 4), "ms_best": round(best, 4),
+                              "Gpts2_per_s": round(evals / med / 1e6, 1),
+                              "tflops_8flop": round(8 * evals / med / 1e9, 2),
+                              "frac_fp32_peak": round(8 * evals / med / 1e9 / peak, 3)}))
+        lib.houv_set_nn_variant(-1)
+        gd1, gd2 = torch.rand(B, N, device="cuda"), torch.rand(B, M, device="cuda")
+        g1, g2 = torch.zeros_like(x1), torch.zeros_like(x2)
+        med, best = timeit(lambda: chamfer_3D.backward(x1, x2, g1, g2, gd1, gd2, i1, i2),
+                           flush=flush)
+        byts = 32.0 * B * (N + M)
+        print(json.dumps({"case": name, "kernel": "K2 bwd", "ms_median": round(med, 4),
+                          "GBps": round(byts / med / 1e6, 1)}))
+
+
+if __name__ == "__main__":
+    {"probe": cmd_probe, "chamfer": cmd_chamfer}[sys.argv[1] if len(sys.argv) > 1 else "probe"]()
