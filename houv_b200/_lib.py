@@ -10,6 +10,7 @@ _LIB = None
 
 _vp = ctypes.c_void_p
 _ci = ctypes.c_int
+_cf = ctypes.c_float
 
 # name -> argtypes; every entry point returns int (0 = ok) unless noted
 _SIGNATURES = {
@@ -17,6 +18,8 @@ _SIGNATURES = {
     "houv_nn_search": [_vp, _vp, _ci, _ci, _ci, _vp, _vp, _vp],
     "houv_chamfer3d_backward": [_vp, _vp, _vp, _vp, _vp, _vp, _ci, _ci, _ci, _vp, _vp, _vp],
     "houv_set_nn_variant": [_ci],
+    "houv_pose_optimise": [_vp, _vp, _ci, _ci, _ci, _ci, _vp, _vp, _vp, _ci, _ci, _ci,
+                           _cf, _cf, _cf, _cf, _cf, _cf, _cf, _cf, _vp, _vp, _vp, _vp, _vp, _vp],
     "houv_fp32_probe": [_vp, _ci, _ci, ctypes.POINTER(ctypes.c_double), _vp],
 }
 

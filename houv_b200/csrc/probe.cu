@@ -57,7 +57,8 @@ extern "C" int houv_fp32_probe(float *scratch, int iters, int packed, double *fl
         probe_kernel<true><<<kProbeCtas, kProbeThreads, 0, (cudaStream_t)stream>>>(scratch, iters);
     else
         probe_kernel<false><<<kProbeCtas, kProbeThreads, 0, (cudaStream_t)stream>>>(scratch, iters);
-    // 64 FFMA lane-ops per thread per iteration in both flavours, 2 FLOP each
-    if (flop_host) *flop_host = 2.0 * 64.0 * (double)iters * kProbeThreads * kProbeCtas;
+    // per thread and iteration: 64 FFMA (scalar) or 64 FFMA2 = 128 lane-FMAs (packed)
+    if (flop_host)
+        *flop_host = 2.0 * (packed ? 128.0 : 64.0) * (double)iters * kProbeThreads * kProbeCtas;
     return check_launch();
 }

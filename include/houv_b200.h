@@ -59,11 +59,35 @@ int houv_chamfer3d_backward(const float *xyz1, const float *xyz2, const float *g
                             const float *graddist2, const int *idx1, const int *idx2, int B,
                             int N, int M, float *gradxyz1, float *gradxyz2, void *stream);
 
+/* Fused multi-start pose optimisation (K3): `iters` iterations of
+ *   HOUV.forward -> Predict_loss -> backward -> Adam.step      (houv.py:120-126)
+ * for rows = P*K independent starts; row r optimises pair r / K (the K starts of a
+ * pair are consecutive rows, as predict_model lays them out, houv.py:111-114).
+ *   src[P,N,3], tgt[P,M,3]   the pairs (N == M <= 2048)
+ *   params[rows,8]           in: initial V_c[3], angle_c, tran_c[3], tran_s (reset_weight,
+ *                            houv.py:40-61, drawn on the host); out: values after `iters` steps
+ *   adam_m, adam_v[rows,8]   in/out Adam moments, or NULL (= start from zero, not returned)
+ *   step0                    Adam steps already taken (0 for a fresh run; allows resume)
+ *   angle_base               0..3: 45-degree window offset of the rotation angle (houv.py:96)
+ *   lr, beta1, beta2, eps    torch.optim.Adam hyper-parameters (reference: 0.01, .9, .999, 1e-8)
+ *   grad_scale               d(mean over the batch)/d(row) = 1/rows_in_batch (houv.py:124)
+ *   percent, w3d, wview      trimmed fraction of the 3-D term (0.5) and the 6 / 1 weights (houv.py:222)
+ *   min1_out[rows], R_out[rows,9], T_out[rows,3]  of the LAST forward, i.e. after iters-1
+ *                            steps, exactly what predict_model returns (houv.py:134-138)
+ *   loss_out[rows] or NULL   full loss 6*min_1 + views of the last forward
+ *   trace[iters,rows,2] or NULL  (loss, min_1) of every forward */
+int houv_pose_optimise(const float *src, const float *tgt, int P, int N, int M, int K,
+                       float *params, float *adam_m, float *adam_v, int step0, int iters,
+                       int angle_base, float lr, float beta1, float beta2, float eps,
+                       float grad_scale, float percent, float w3d, float wview,
+                       float *min1_out, float *loss_out, float *R_out, float *T_out,
+                       float *trace, void *stream);
+
 /* Tuning knob for the NN kernel shape: variant 0..3 = (queries/thread, threads/CTA)
  * (2,128) (4,128) (4,64) (2,256); -1 = built-in default.  Returns the old value. */
 int houv_set_nn_variant(int variant);
 
-/* FP32 CUDA-core peak probe: runs `iters` x 64 dependent-free FFMA per thread on a
+/* FP32 CUDA-core peak probe: runs `iters` x 64 FFMA (or FFMA2 when packed) per thread on a
  * full-chip grid; *flop_host receives the FLOP it executed (2 per FFMA lane-op).
  * Time it with events around the call to get the roofline denominator. */
 int houv_fp32_probe(float *scratch /* >= 4 floats */, int iters, int packed,

@@ -1,0 +1,127 @@
+"""DEV-CONTAINER ONLY (needs /root/reference).  Imports the reference's HOUV
+python files UNMODIFIED on a GPU-less host so that golden vectors can be made
+from the reference's own code:
+
+  registration/models/houv.py, registration/model_utils_completion.py,
+  registration/train_utils.py, registration/model_utils.py (SVDHead)
+
+What is stubbed, and only that:
+  * `.cuda()` on tensors/modules becomes the identity (houv.py:64,67,76,
+    model_utils_completion.py:159 hard-code it);
+  * `metrics.cd` (the JIT CUDA extension, utils/metrics/CD/chamfer3D) is served
+    by the reference's own kernel SOURCE compiled for the host
+    (oracle/_ref/libref_chamfer.so) wrapped in the same autograd Function shape
+    as dist_chamfer_3D.py:26-64; `metrics.fscore` is the reference's fscore.py;
+  * absent third-party imports that the hot path never calls (mm3d_pn2/mmcv,
+    emd, visu_utils/matplotlib/open3d, models.simple_icp) are empty modules.
+"""
+import importlib.util
+import os
+import sys
+import types
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+REF = "/root/reference"
+REG = os.path.join(REF, "registration")
+
+_loaded = {}
+
+
+class _RefChamferFunction(torch.autograd.Function):
+    """dist_chamfer_3D.py:26-64 with chamfer_3D.forward/backward served by the
+    host build of the reference kernels."""
+
+    @staticmethod
+    def forward(ctx, xyz1, xyz2):
+        from oracle import chamfer as oc
+        d1, d2, i1, i2 = oc.ref_chamfer_forward(xyz1.detach().numpy(), xyz2.detach().numpy())
+        dist1, dist2 = torch.from_numpy(d1), torch.from_numpy(d2)
+        idx1, idx2 = torch.from_numpy(i1), torch.from_numpy(i2)
+        ctx.save_for_backward(xyz1, xyz2, idx1, idx2)
+        return dist1, dist2, idx1, idx2
+
+    @staticmethod
+    def backward(ctx, graddist1, graddist2, gradidx1, gradidx2):
+        from oracle import chamfer as oc
+        xyz1, xyz2, idx1, idx2 = ctx.saved_tensors
+        g1, g2 = oc.ref_chamfer_backward(xyz1.detach().numpy(), xyz2.detach().numpy(),
+                                         graddist1.contiguous().numpy(),
+                                         graddist2.contiguous().numpy(), idx1.numpy(), idx2.numpy())
+        return torch.from_numpy(g1), torch.from_numpy(g2)
+
+
+class _RefChamferDist(torch.nn.Module):
+    def forward(self, input1, input2):
+        return _RefChamferFunction.apply(input1.contiguous().float(), input2.contiguous().float())
+
+
+def _file_module(name, path):
+    spec = importlib.util.spec_from_file_location(name, path)
+    mod = importlib.util.module_from_spec(spec)
+    sys.modules[name] = mod
+    spec.loader.exec_module(mod)
+    return mod
+
+
+class _Anything(types.ModuleType):
+    def __getattr__(self, k):
+        if k.startswith("__"):
+            raise AttributeError(k)
+        return None
+
+
+def load():
+    """-> dict(houv=<module>, muc=<model_utils_completion>, tu=<train_utils>)."""
+    if _loaded:
+        return _loaded
+    torch.Tensor.cuda = lambda self, *a, **k: self
+    torch.nn.Module.cuda = lambda self, *a, **k: self
+
+    fscore_mod = _file_module("ref_fscore", os.path.join(REF, "utils/metrics/CD/fscore.py"))
+    metrics = types.ModuleType("metrics")
+    metrics.cd = _RefChamferDist
+    metrics.fscore = fscore_mod.fscore
+    metrics.emd = None
+    sys.modules["metrics"] = metrics
+    for name in ("mm3d_pn2", "visu_utils", "models", "models.simple_icp", "open3d"):
+        if name not in sys.modules:
+            sys.modules[name] = _Anything(name)
+    sys.path.insert(0, REG)
+    cwd = os.getcwd()
+    os.chdir(REG)
+    try:
+        muc = _file_module("model_utils_completion", os.path.join(REG, "model_utils_completion.py"))
+        tu = _file_module("train_utils", os.path.join(REG, "train_utils.py"))
+        houv = _file_module("ref_houv", os.path.join(REG, "models/houv.py"))
+    finally:
+        os.chdir(cwd)
+    _loaded.update(houv=houv, muc=muc, tu=tu)
+    return _loaded
+
+
+def load_svdhead():
+    """registration/model_utils.py imports open3d & co. at the top; SVDHead only
+    needs torch, so exec the class source alone (text is read, not copied)."""
+    import ast
+    src = open(os.path.join(REG, "model_utils.py")).read()
+    tree = ast.parse(src)
+    node = [n for n in tree.body if isinstance(n, ast.ClassDef) and n.name == "SVDHead"][0]
+    ns = {"torch": torch, "nn": torch.nn}
+    exec(compile(ast.Module(body=[node], type_ignores=[]), "model_utils.py:SVDHead", "exec"), ns)
+    return ns["SVDHead"]
+
+
+if __name__ == "__main__":
+    m = load()
+    torch.manual_seed(0)
+    np.random.seed(0)
+    src = torch.rand(1, 64, 3) - 0.5
+    tgt = torch.rand(1, 64, 3) - 0.5
+    net = m["houv"].HOUV(32, 0)  # reset_weight needs >= 26 rows (houv.py:43-51)
+    loss, R, T = m["houv"].predict_model(net, src, tgt, kernel=32, num_epochs=3)
+    print(loss, R.shape, T.shape)
