@@ -1,0 +1,329 @@
+#!/usr/bin/env python
+"""Contract benchmark: registered pairs/sec for full HOUV registration
+(BASELINE.json metric) on N B200s of one node.
+
+    python bench.py [--gpus N --steps K --warmup W] [--impl reference]
+    torchrun ... bench.py --gpus N ...          (one rank per GPU, NCCL)
+
+A "step" registers this rank's shard of the synthetic MVP-shaped set with
+solve_model semantics (64 starts x 200 Adam iterations at angle_base 0, retries
+at angle_base 1..3 for pairs whose best min_1 stays above 0.030, best start ->
+4x4 pose) and gathers poses + metrics from all ranks (the path's only
+collective).  Weak scaling: every rank holds --pairs-per-gpu pairs (150 = the
+1200-pair set of BASELINE config 4 on 8 GPUs; at N=1 it is pairs 0..149).
+
+`value`      pairs/s with the clouds already resident in HBM.
+`e2e`        pairs/s through the public API (shard.register_pairs) from PINNED
+             HOST buffers: H2D of the clouds and D2H of poses+metrics inside the
+             timed region, every step.
+`roofline`   the dominant kernel (K3 pose_kernel) against the FP32 CUDA-core
+             peak measured live by an FFMA probe ("bound": "fp32" -- K=3 distance
+             evaluation is neither HBM- nor tensor-bound).
+`cpu_baseline` / --impl reference: the CPU oracle of the same path (restated
+             houv.py over the multi-threaded C chamfer oracle) on the box's host
+             cores, on a bounded sample, linearly extrapolated (stated in `sample`).
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+N_POINTS = 2048
+KERNEL = 64
+ITERS = 200
+BATCH = 50
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=2)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--pairs-per-gpu", type=int, default=150)
+    ap.add_argument("--iters", type=int, default=ITERS, help="Adam iterations (reference: 200)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                 "--format=csv,noheader,nounits", "-lms", "200"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.th = threading.Thread(target=self._pump, daemon=True)
+            self.th.start()
+        except OSError:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons, power = [], [], set(), []
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2])); power.append(float(f[3]))
+            except ValueError:
+                continue
+            for n, v in zip(names, f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": statistics.median(sm) if sm else None,
+                "sm_max_mhz": max(mx) if mx else None,
+                "power_w_max": max(power) if power else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ----------------------------------------------------------------- CPU arm
+def cpu_houv_sample(n_iters, threads):
+    """One bounded sample of the reference's path on the host: ONE pair, 64 starts,
+    `n_iters` of the 200 Adam iterations at angle_base 0, through the CPU oracle
+    (oracle/houv.py restates registration/models/houv.py; its Chamfer kernels are
+    oracle/chamfer_oracle.c on `threads` host threads).  Returns seconds."""
+    import torch
+    from houv_b200 import synth
+    from oracle import chamfer as oc
+    from oracle import houv as oh
+    oc.set_threads(threads)
+    s, t, _ = synth.make_pairs(0, 1, n_points=N_POINTS)
+    src, tgt = torch.from_numpy(s), torch.from_numpy(t)
+    t0 = time.perf_counter()
+    oh.predict_model(oh.HOUV(), src, tgt, kernel=KERNEL, num_epochs=n_iters, angle_base=0)
+    return time.perf_counter() - t0
+
+
+def cpu_pairs_per_s(seconds, n_iters):
+    """Linear extrapolation of the sample to a full 200-iteration angle_base-0 solve of one
+    pair.  Retries (x(1+3p)) are NOT added, which flatters the CPU arm."""
+    return 1.0 / (seconds * ITERS / n_iters)
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return  # rank 0 alone runs the CPU arm
+    import torch
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    n_it = 5
+    for _ in range(args.warmup):
+        cpu_houv_sample(1, cores)
+    ts = [cpu_houv_sample(n_it, cores) for _ in range(args.steps)]
+    sec = sum(ts) / len(ts)
+    val = cpu_pairs_per_s(sec, n_it)
+    sample = ("each step = 1 pair x %d starts x %d of %d Adam iterations at angle_base 0 "
+              "(2048x2048 pts, 8 directed NN searches + backward per iteration); pairs/s = "
+              "1/(t_step*%d/%d), retries not added" % (KERNEL, n_it, ITERS, ITERS, n_it))
+    print(json.dumps({
+        "impl": "reference", "metric": "registered pairs/sec (2048-pt, HOUV full)",
+        "value": val, "unit": "pairs/s", "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": sec * 1e3, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": workload_config(args),
+        "cpu_baseline": {"value": val, "unit": "pairs/s", "cores": cores, "kind": "port",
+                         "sample": sample},
+        "e2e": {"value": val, "unit": "pairs/s", "h2d_bytes_per_step": 0,
+                "d2h_bytes_per_step": 0}}))
+
+
+def workload_config(args):
+    return {"workload": "C4 shard: full HOUV solve_model, %d pairs/GPU (1200-pair "
+                        "MVP_ExtraTest_RG-shaped set at 8 GPUs), 2048x2048 pts, %d starts x %d "
+                        "its + angle_base 1-3 retries above 0.030" %
+                        (args.pairs_per_gpu, KERNEL, args.iters),
+            "pairs_per_gpu": args.pairs_per_gpu, "batch_size": BATCH, "starts": KERNEL,
+            "iters": args.iters, "points": N_POINTS, "parallelism": "pairs sharded, dp%d" % args.gpus,
+            "l2": "256 MB buffer written between timed steps (L2 flush)"}
+
+
+# ----------------------------------------------------------------- GPU arm
+def run_ours(args):
+    import ctypes
+    import numpy as np
+    import torch
+    from houv_b200 import _lib, shard, solver, synth
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: houv_b200 has no CPU path")
+    rank, world, local = shard.init_distributed()
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    lib = _lib.load()
+    P = args.pairs_per_gpu
+    first = rank * P
+    s, t, tr = synth.make_pairs(first, P, n_points=N_POINTS)
+    # host side of the public API: pinned buffers
+    h_src = torch.from_numpy(s).pin_memory()
+    h_tgt = torch.from_numpy(t).pin_memory()
+    h_gt = torch.from_numpy(tr).pin_memory()
+    h_out = torch.empty(P * world, 19).pin_memory()
+    d_src, d_tgt, d_gt = h_src.to(dev), h_tgt.to(dev), h_gt.to(dev)
+    flush = torch.zeros(64 * 1024 * 1024, device=dev)  # 256 MB > 126 MB L2
+
+    def step_device():
+        ans, met = shard.register_pairs(d_src, d_tgt, d_gt, batch_size=BATCH, kernel=KERNEL,
+                                        num_epochs=args.iters)
+        return shard.gather_results(ans, met, world)
+
+    def step_e2e():
+        a = h_src.to(dev, non_blocking=True)
+        b = h_tgt.to(dev, non_blocking=True)
+        g = h_gt.to(dev, non_blocking=True)
+        ans, met = shard.register_pairs(a, b, g, batch_size=BATCH, kernel=KERNEL,
+                                        num_epochs=args.iters)
+        ans, met = shard.gather_results(ans, met, world)
+        h_out.copy_(torch.cat([ans.reshape(-1, 16), met], dim=1), non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        return ans, met
+
+    def barrier():
+        if world > 1:
+            torch.distributed.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        """device time of `steps` steps: CUDA events, barrier + synchronize on both sides,
+        L2 flushed before every step (outside the per-step event pair), max over ranks."""
+        total = 0.0
+        out = None
+        for _ in range(steps):
+            flush.add_(1.0)
+            barrier()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            out = fn()
+            e1.record()
+            barrier()
+            total += e0.elapsed_time(e1)
+        tt = torch.tensor([total], device=dev, dtype=torch.float64)
+        if world > 1:
+            torch.distributed.all_reduce(tt, op=torch.distributed.ReduceOp.MAX)
+        return float(tt.item()), out
+
+    # FP32 roofline denominator, measured on this GPU right now
+    scratch = torch.zeros(16, device=dev)
+    flop = ctypes.c_double(0)
+    best = 1e30
+    for i in range(6):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        _lib.check(lib.houv_fp32_probe(scratch.data_ptr(), 4096, 0, ctypes.byref(flop),
+                                       _lib.stream_ptr()), "probe")
+        e1.record()
+        torch.cuda.synchronize()
+        if i >= 2:
+            best = min(best, e0.elapsed_time(e1))
+    fp32_peak = flop.value / best / 1e9  # TFLOP/s
+
+    for _ in range(args.warmup):
+        step_device()
+    barrier()
+
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    solver.KERNEL_TIMING = []
+    launches0 = _lib.LAUNCHES[0]
+    ms_dev, (ans, met) = timed(step_device, args.steps)
+    launches = _lib.LAUNCHES[0] - launches0
+    ktim = solver.KERNEL_TIMING
+    solver.KERNEL_TIMING = None
+    ms_e2e, _ = timed(step_e2e, args.steps)
+    clocks = sampler.stop() if rank == 0 else None
+
+    # dominant kernel: executed FLOP = 2 directions x N*M x 13 FLOP per row-iteration
+    kms = sum(a.elapsed_time(b) for a, b, *_ in ktim)
+    kflop = sum(26.0 * n * n * rows * iters for _, _, rows, iters, n in ktim)
+    kref = sum(64.0 * n * n * rows * iters for _, _, rows, iters, n in ktim)
+    if rank != 0:
+        return
+    total_pairs = P * world * args.steps
+    value = total_pairs / (ms_dev / 1e3)
+    e2e = total_pairs / (ms_e2e / 1e3)
+    met = met.float().cpu().numpy()
+    traffic = None
+    tfile = os.path.join(ROOT, "profiles", "k3_traffic.json")
+    if os.path.exists(tfile):
+        traffic = json.load(open(tfile)).get("dram_bytes_per_launch")
+    line = {
+        "metric": "registered pairs/sec (2048-pt, HOUV full)", "value": value, "unit": "pairs/s",
+        "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms_dev / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": workload_config(args),
+        "e2e": {"value": e2e, "unit": "pairs/s", "ms_per_step": ms_e2e / args.steps,
+                "h2d_bytes_per_step": int(h_src.numel() * 4 * 2 + h_gt.numel() * 4),
+                "d2h_bytes_per_step": int(h_out.numel() * 4)},
+        "gpu_launches": launches,
+        "roofline": {"bound": "fp32", "kernel": "houv::pose_kernel (K3)",
+                     "achieved": kflop / kms / 1e9, "peak": fp32_peak, "unit": "TFLOP/s",
+                     "frac": kflop / kms / 1e9 / fp32_peak, "traffic": traffic,
+                     "peak_source": "FFMA-chain probe run in this process (MEASURED_PEAKS.json "
+                                    "holds no FP32 CUDA-core figure)",
+                     "ref_equiv_tflops": kref / kms / 1e9,
+                     "kernel_ms_per_launch": kms / max(len(ktim), 1),
+                     "kernel_share_of_step": kms / ms_dev,
+                     "flop_per_launch": kflop / max(len(ktim), 1)},
+        "clocks": clocks,
+        "quality": {"rot_err_deg_mean": float(met[:, 0].mean()),
+                    "rot_err_deg_median": float(np.median(met[:, 0])),
+                    "trans_err_mean": float(met[:, 1].mean()),
+                    "mse_mean": float(met[:, 2].mean())},
+    }
+    if world == 1 and not args.no_cpu_baseline:
+        cores = os.cpu_count() or 1
+        torch.set_num_threads(cores)
+        cpu_houv_sample(1, cores)
+        n_it = 4
+        sec = cpu_houv_sample(n_it, cores)
+        line["cpu_baseline"] = {
+            "value": cpu_pairs_per_s(sec, n_it), "unit": "pairs/s", "cores": cores,
+            "kind": "port",
+            "sample": "1 pair x %d starts x %d of %d Adam iterations at angle_base 0 in %.1f s "
+                      "(CPU oracle: restated houv.py over the C chamfer oracle on %d threads), "
+                      "linearly extrapolated, retries not added" % (KERNEL, n_it, ITERS, sec, cores)}
+    print(json.dumps(line))
+
+
+if __name__ == "__main__":
+    a = parse()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_ours(a)
+    try:
+        import torch
+        if torch.distributed.is_available() and torch.distributed.is_initialized():
+            torch.distributed.destroy_process_group()
+    except Exception:
+        pass

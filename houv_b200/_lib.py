@@ -19,7 +19,8 @@ _SIGNATURES = {
     "houv_chamfer3d_backward": [_vp, _vp, _vp, _vp, _vp, _vp, _ci, _ci, _ci, _vp, _vp, _vp],
     "houv_set_nn_variant": [_ci],
     "houv_pose_optimise": [_vp, _vp, _ci, _ci, _ci, _ci, _vp, _vp, _vp, _ci, _ci, _ci,
-                           _cf, _cf, _cf, _cf, _cf, _cf, _cf, _cf, _vp, _vp, _vp, _vp, _vp, _vp],
+                           _cf, _cf, _cf, _cf, _cf, _cf, _cf, _cf, _vp, _vp, _vp, _vp, _vp, _vp, _vp,
+                           _ci, _vp],
     "houv_fp32_probe": [_vp, _ci, _ci, ctypes.POINTER(ctypes.c_double), _vp],
 }
 
@@ -48,6 +49,13 @@ def load():
 
 class HouvError(RuntimeError):
     pass
+
+
+LAUNCHES = [0]  # kernel launches issued through the C ABI (bench.py reports them)
+
+
+def count_launches(n=1):
+    LAUNCHES[0] += n
 
 
 def check(code, what):

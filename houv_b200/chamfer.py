@@ -31,6 +31,7 @@ class _Chamfer3DModule:
                 xyz1.data_ptr(), xyz2.data_ptr(), B, N, M, dist1.data_ptr(), dist2.data_ptr(),
                 idx1.data_ptr(), idx2.data_ptr(), _lib.stream_ptr())
         _lib.check(rc, "houv_chamfer3d_forward")
+        _lib.count_launches(1)
         return 1
 
     @staticmethod
@@ -43,6 +44,7 @@ class _Chamfer3DModule:
                 idx1.data_ptr(), idx2.data_ptr(), B, N, M, gradxyz1.data_ptr(),
                 gradxyz2.data_ptr(), _lib.stream_ptr())
         _lib.check(rc, "houv_chamfer3d_backward")
+        _lib.count_launches(1)
         return 1
 
 
@@ -117,6 +119,7 @@ def nn_search(query, target):
         rc = _lib.load().houv_nn_search(query.data_ptr(), target.data_ptr(), B, N, M,
                                         dist.data_ptr(), idx.data_ptr(), _lib.stream_ptr())
     _lib.check(rc, "houv_nn_search")
+    _lib.count_launches(1)
     return dist, idx
 
 

@@ -48,6 +48,8 @@ struct PoseArgs {
     float *R_out;       // [rows,9]
     float *T_out;       // [rows,3]
     float *trace;       // [iters,rows,2] (loss, min_1) per forward, or null
+    const int *row_pair;  // [rows] pair of each row, or null (= row / K)
+    const int *row_base;  // [rows] angle_base of each row, or null (= angle_base)
     int P, N, M, K, rows;
     int step0, iters, angle_base, k3d;
     float lr, beta1, beta2, eps, grad_scale, w3d, wview;
@@ -261,7 +263,7 @@ __global__ void __launch_bounds__(kThreads, 2) pose_kernel(const PoseArgs A) {
     Smem &S = *reinterpret_cast<Smem *>(smem_raw);
     const int t = threadIdx.x;
     const int row = blockIdx.x;
-    const int pair = row / A.K;
+    const int pair = A.row_pair ? A.row_pair[row] : row / A.K;
     const int N = A.N, M = A.M;
     const int Npad = (N + kG - 1) / kG * kG, Mpad = (M + kG - 1) / kG * kG;
     const float *src = A.src + (size_t)pair * N * 3;
@@ -291,7 +293,8 @@ __global__ void __launch_bounds__(kThreads, 2) pose_kernel(const PoseArgs A) {
         b2t = pow((double)A.beta2, (double)A.step0);
     }
     // angle_base*pi/4 evaluated in double and rounded once, as python does (houv.py:96)
-    const float boff = (float)((double)A.angle_base * 3.14159274101257324 / 4.0);
+    const int abase = A.row_base ? A.row_base[row] : A.angle_base;
+    const float boff = (float)((double)abase * 3.14159274101257324 / 4.0);
     const int k3d = A.k3d;
 
     for (int it = 0; it < A.iters; ++it) {
@@ -538,9 +541,13 @@ extern "C" int houv_pose_optimise(const float *src, const float *tgt, int P, int
                                   int iters, int angle_base, float lr, float beta1, float beta2,
                                   float eps, float grad_scale, float percent, float w3d,
                                   float wview, float *min1_out, float *loss_out, float *R_out,
-                                  float *T_out, float *trace, void *stream) {
-    if (P < 0 || N <= 0 || M <= 0 || K <= 0 || iters < 0 || step0 < 0) return HOUV_E_BADARG;
-    if (P == 0 || iters == 0) return 0;
+                                  float *T_out, float *trace, const int *row_pair,
+                                  const int *row_base, int rows, void *stream) {
+    if (P < 0 || N <= 0 || M <= 0 || K <= 0 || iters < 0 || step0 < 0 || rows < 0)
+        return HOUV_E_BADARG;
+    if (rows == 0) rows = P * K;
+    if (rows != P * K && !row_pair) return HOUV_E_BADARG;
+    if (P == 0 || iters == 0 || rows == 0) return 0;
     if (!src || !tgt || !params || !min1_out || !R_out || !T_out) return HOUV_E_BADARG;
     if (N > kPts || M > kPts) return HOUV_E_TOOBIG;
     // calc_cd_percent takes k = int(points*percent) from BOTH lists and the view terms use
@@ -549,8 +556,8 @@ extern "C" int houv_pose_optimise(const float *src, const float *tgt, int P, int
     PoseArgs a;
     a.src = src; a.tgt = tgt; a.params = params; a.adam_m = adam_m; a.adam_v = adam_v;
     a.min1_out = min1_out; a.loss_out = loss_out; a.R_out = R_out; a.T_out = T_out;
-    a.trace = trace;
-    a.P = P; a.N = N; a.M = M; a.K = K; a.rows = P * K;
+    a.trace = trace; a.row_pair = row_pair; a.row_base = row_base;
+    a.P = P; a.N = N; a.M = M; a.K = K; a.rows = rows;
     a.step0 = step0; a.iters = iters; a.angle_base = angle_base;
     a.k3d = (int)((double)N * (double)percent);
     if (a.k3d < 1 || a.k3d > N) return HOUV_E_BADARG;

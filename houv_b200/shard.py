@@ -1,0 +1,81 @@
+"""Multi-GPU driver: independent pairs sharded by contiguous index range, one
+process per GPU, no traffic during the optimisation, ONE all-gather of the
+per-pair poses and metrics at the end.
+
+Replaces the reference's 4-background-jobs + .npy files + `sleep 600` + combine
+scheme (/root/reference/registration/run_test.sh:6,21-23;
+test_mult.py:34,65-66,70-81; dataset.py:354-372 MVP_RG_rotated_bound(l, r)).
+
+Batching follows the reference's DataLoader (cfgs/houv.yaml:1 batch_size,
+train_HOUV.py:69,100-112): each rank walks its range in batches and calls
+solve_model per batch.  A pair's result depends on the batch it sits in
+(initial values are drawn per batch row, houv.py:116, and the loss is the mean
+over the batch, :124), so results are independent of the number of GPUs exactly
+when `batch_size` divides the per-rank range -- the launcher checks that.
+"""
+import os
+
+import torch
+
+from . import solver
+from .loss import rmse_loss, rotation_error, translation_error
+
+
+def shard_range(total, rank, world):
+    """Contiguous [l, r) of `total` pairs for `rank` (test_mult.py's -l/-r)."""
+    per = (total + world - 1) // world
+    l = min(rank * per, total)
+    return l, min(l + per, total)
+
+
+def init_distributed(backend=None):
+    """torchrun environment -> (rank, world, local_rank); no-op for one process."""
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world > 1 and not torch.distributed.is_initialized():
+        if backend is None:
+            backend = "nccl" if torch.cuda.is_available() else "gloo"
+        torch.distributed.init_process_group(backend=backend)
+    return rank, world, local
+
+
+def register_pairs(src, tgt, transform=None, batch_size=50, kernel=64, num_epochs=200,
+                   solve=None):
+    """Full HOUV registration (solve_model semantics) of src[P,N,3] -> tgt[P,N,3] in
+    batches.  -> ans[P,4,4] and, when the ground truth is given, metrics[P,3] =
+    (rotation error deg, translation error, mse) as train_HOUV.py:112-118 logs them."""
+    solve = solve or solver.solve_model
+    P = src.shape[0]
+    net = None
+    ans_all, met_all = [], []
+    for l in range(0, P, batch_size):
+        r = min(l + batch_size, P)
+        if net is None:
+            net = solver.HOUV((r - l) * kernel, 0, device=src.device)
+        ans = solve(net, src[l:r], tgt[l:r], None, kernel=kernel, num_epochs=num_epochs,
+                    prefix='device')
+        ans_all.append(ans)
+        if transform is not None:
+            gt = transform[l:r]
+            met_all.append(torch.stack([
+                rotation_error(ans[:, :3, :3], gt[:, :3, :3]),
+                translation_error(ans[:, :3, 3], gt[:, :3, 3]),
+                rmse_loss(src[l:r], ans, gt)], dim=1))
+    ans = torch.cat(ans_all) if ans_all else torch.zeros(0, 4, 4, device=src.device)
+    met = torch.cat(met_all) if met_all else None
+    return ans, met
+
+
+def gather_results(ans, metrics, world):
+    """The only collective of the path: all_gather of [P_local, 16+3] floats
+    (NCCL over NVLink on GPUs, gloo in the CPU tests).  Ranks hold equal counts."""
+    packed = torch.cat([ans.reshape(ans.shape[0], 16),
+                        metrics if metrics is not None else ans.new_zeros(ans.shape[0], 3)], dim=1)
+    packed = packed.contiguous()
+    if world > 1:
+        out = packed.new_empty(world * packed.shape[0], packed.shape[1])
+        torch.distributed.all_gather_into_tensor(out, packed)
+    else:
+        out = packed
+    return out[:, :16].reshape(-1, 4, 4), out[:, 16:]

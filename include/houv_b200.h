@@ -75,13 +75,19 @@ int houv_chamfer3d_backward(const float *xyz1, const float *xyz2, const float *g
  *   min1_out[rows], R_out[rows,9], T_out[rows,3]  of the LAST forward, i.e. after iters-1
  *                            steps, exactly what predict_model returns (houv.py:134-138)
  *   loss_out[rows] or NULL   full loss 6*min_1 + views of the last forward
- *   trace[iters,rows,2] or NULL  (loss, min_1) of every forward */
+ *   trace[iters,rows,2] or NULL  (loss, min_1) of every forward
+ *   row_pair[rows] or NULL   pair optimised by each row (default row / K); with it `rows` may
+ *                            differ from P*K, e.g. the three retry passes of solve_model
+ *                            (houv.py:168-169) in one launch
+ *   row_base[rows] or NULL   per-row angle_base overriding the scalar
+ *   rows                     number of rows; 0 = P*K */
 int houv_pose_optimise(const float *src, const float *tgt, int P, int N, int M, int K,
                        float *params, float *adam_m, float *adam_v, int step0, int iters,
                        int angle_base, float lr, float beta1, float beta2, float eps,
                        float grad_scale, float percent, float w3d, float wview,
                        float *min1_out, float *loss_out, float *R_out, float *T_out,
-                       float *trace, void *stream);
+                       float *trace, const int *row_pair, const int *row_base, int rows,
+                       void *stream);
 
 /* Tuning knob for the NN kernel shape: variant 0..3 = (queries/thread, threads/CTA)
  * (2,128) (4,128) (4,64) (2,256); -1 = built-in default.  Returns the old value. */

@@ -1,0 +1,165 @@
+"""GPU parity of the fused pose-optimisation kernel K3 (houv_pose_optimise,
+through the C ABI) against the CPU oracle (oracle/houv.py = restated
+registration/models/houv.py, pinned to the reference's own python files).
+
+SURVEY.md section 7, hard part 1: the optimiser is chaotic (arg-min switches,
+hard min, top-k membership), so parity is stated per horizon:
+  (i)   one forward: loss / min_1 / R / T                 <= 1e-5 relative
+  (ii)  one backward: all 8 gradients (from Adam's m)      <= 1e-4 of the row's gradient norm
+  (iii) short trajectories T in {5, 20}: loss trace        <= 1e-4 / 2e-3 relative
+  (iv)  solve_model end state on well-conditioned pairs: rotation within 1e-4 rad,
+        translation within 1e-5 of the oracle's selected start.
+"""
+import numpy as np
+import pytest
+import torch
+
+from houv_b200 import synth
+from oracle import houv as oh
+
+pytestmark = pytest.mark.gpu
+
+N_SMALL = 256
+KERNEL = 32
+
+
+def _pairs(first, count, n=N_SMALL):
+    s, t, tr = synth.make_pairs(first, count, n_points=n)
+    return torch.from_numpy(s), torch.from_numpy(t), torch.from_numpy(tr)
+
+
+def _oracle_trace(src, tgt, iters, angle_base=0, kernel=KERNEL):
+    trace = []
+    net = oh.HOUV()
+    out = oh.predict_model(net, src, tgt, kernel=kernel, num_epochs=iters, angle_base=angle_base,
+                           trace=trace)
+    return trace, out, net
+
+
+def _gpu_run(src, tgt, iters, angle_base=0, kernel=KERNEL, **kw):
+    from houv_b200 import solver
+    rows = src.shape[0] * kernel
+    params = torch.from_numpy(solver.initial_parameters(rows)).cuda()
+    m = torch.zeros(rows, 8).cuda()
+    v = torch.zeros(rows, 8).cuda()
+    out = solver.pose_optimise(src.cuda(), tgt.cuda(), params, kernel, iters, angle_base=angle_base,
+                               adam_m=m, adam_v=v, want_loss=True, want_trace=True, **kw)
+    return out, params, m, v
+
+
+def _rel(a, b):
+    a, b = np.asarray(a, np.float64), np.asarray(b, np.float64)
+    return np.abs(a - b).max() / max(np.abs(b).max(), 1e-30)
+
+
+def test_initial_parameters_match_oracle():
+    from houv_b200 import solver
+    p = solver.initial_parameters(100)
+    vc, ac, tc, ts = oh.initial_parameters(100)
+    assert np.array_equal(p, np.concatenate([vc, ac, tc, ts], 1))
+    assert np.array_equal(solver.initial_parameters(64), p[:64])  # row i independent of rows
+
+
+@pytest.mark.parametrize("angle_base", [0, 2])
+def test_single_forward(angle_base):
+    src, tgt, _ = _pairs(0, 2)
+    trace, (l, R, T), _ = _oracle_trace(src, tgt, 1, angle_base)
+    out, *_ = _gpu_run(src, tgt, 1, angle_base)
+    assert _rel(out["trace"][0, :, 0].cpu(), trace[0]["loss"]) < 1e-5
+    assert _rel(out["trace"][0, :, 1].cpu(), trace[0]["min_1"]) < 1e-5
+    assert _rel(out["min_1"].cpu(), l.detach().reshape(-1)) < 1e-5
+    assert _rel(out["loss"].cpu(), trace[0]["loss"]) < 1e-5
+    assert np.abs(out["R"].cpu().numpy() - R.detach().reshape(-1, 3, 3).numpy()).max() < 2e-6
+    assert np.abs(out["T"].cpu().numpy() - T.detach().reshape(-1, 3).numpy()).max() < 2e-6
+
+
+def test_single_backward_gradients():
+    src, tgt, _ = _pairs(3, 2)
+    trace, _, _ = _oracle_trace(src, tgt, 1)
+    out, params, m, v = _gpu_run(src, tgt, 1)
+    g_gpu = (m / 0.1).cpu().numpy().astype(np.float64)  # m_1 = (1-beta1) * g
+    g_ref = torch.cat(trace[0]["grads"], dim=1).numpy().astype(np.float64)
+    norm = np.linalg.norm(g_ref, axis=1, keepdims=True)
+    err = np.abs(g_gpu - g_ref) / np.maximum(norm, 1e-30)
+    assert err.max() < 1e-4, err.max()
+    # v_1 = (1-beta2) g^2
+    assert _rel(v.cpu().numpy(), 0.001 * g_ref ** 2) < 1e-3
+
+
+def test_adam_first_step_matches_oracle():
+    """p1 = p0 - lr*g/(|g|+eps): compared where |g| >> eps = 1e-8 (elsewhere the update is a
+    steep function of a gradient that is itself only known to ~1e-4 relative)."""
+    src, tgt, _ = _pairs(5, 1)
+    trace, _, net = _oracle_trace(src, tgt, 1)
+    _, params, _, _ = _gpu_run(src, tgt, 1)
+    ref = torch.cat([net.V_c, net.angle_c, net.tran_c, net.tran_s], dim=1).detach().numpy()
+    g_ref = np.abs(torch.cat(trace[0]["grads"], dim=1).numpy())
+    well = g_ref > 1e-5
+    assert well.mean() > 0.5
+    assert np.abs(params.cpu().numpy() - ref)[well].max() < 2e-6
+    assert np.abs(params.cpu().numpy() - ref).max() < 0.0101  # never more than one lr
+
+
+@pytest.mark.parametrize("iters,tol", [(5, 1e-4), (20, 2e-3)])
+def test_short_trajectories(iters, tol):
+    src, tgt, _ = _pairs(7, 2)
+    trace, (l, R, T), _ = _oracle_trace(src, tgt, iters)
+    out, *_ = _gpu_run(src, tgt, iters)
+    ref = np.stack([t["loss"].numpy() for t in trace])  # [iters, rows]
+    got = out["trace"][:, :, 0].cpu().numpy()
+    rel = np.abs(got - ref) / np.abs(ref)
+    # the median row tracks tightly; a few rows may cross an arg-min switch a step apart
+    assert np.median(rel[-1]) < tol, np.median(rel[-1])
+    assert (rel[-1] < 10 * tol).mean() > 0.9
+
+
+def test_last_forward_is_before_last_step():
+    """houv.py:120-138: R, T, min_1 come from the last forward, i.e. after iters-1 steps."""
+    src, tgt, _ = _pairs(9, 1)
+    a, *_ = _gpu_run(src, tgt, 3)
+    b, *_ = _gpu_run(src, tgt, 4)
+    assert torch.equal(a["trace"][2], b["trace"][2])
+    assert torch.equal(a["min_1"], a["trace"][2, :, 1])
+    assert not torch.equal(a["R"], b["R"])
+
+
+def test_resume_equals_one_shot():
+    """Adam state in/out (checkpoint/resume of a row): 3 + 4 steps == 7 steps, bit for bit."""
+    from houv_b200 import solver
+    src, tgt, _ = _pairs(11, 1)
+    one, p1, m1, v1 = _gpu_run(src, tgt, 7)
+    _, p, m, v = _gpu_run(src, tgt, 3)
+    two = solver.pose_optimise(src.cuda(), tgt.cuda(), p, KERNEL, 4, adam_m=m, adam_v=v, step0=3,
+                               want_trace=True)
+    assert torch.equal(p, p1) and torch.equal(m, m1) and torch.equal(v, v1)
+    assert torch.equal(two["trace"], one["trace"][3:])
+
+
+def test_fused_loss_equals_unfused_operator_path():
+    """K3's forward == HOUV.forward + Predict_loss built from the K1 operator (torch ops)."""
+    from houv_b200 import solver
+    src, tgt, _ = _pairs(13, 2, n=512)
+    net = solver.HOUV(2 * KERNEL, 0)
+    net.reset_weight(2 * KERNEL, 1)
+    s = src.cuda().unsqueeze(1).expand(-1, KERNEL, -1, -1).reshape(-1, 512, 3)
+    t = tgt.cuda().unsqueeze(1).expand(-1, KERNEL, -1, -1).reshape(-1, 512, 3)
+    src_temp, R, T = net(s)
+    loss, min_1 = solver.Predict_loss(src_temp, t)
+    params = net.packed().contiguous()
+    out = solver.pose_optimise(src.cuda(), tgt.cuda(), params, KERNEL, 1, angle_base=1,
+                               want_loss=True)
+    assert _rel(out["loss"].cpu(), loss.detach().cpu()) < 1e-5
+    assert _rel(out["min_1"].cpu(), min_1.detach().cpu()) < 1e-5
+
+
+def test_bad_arguments_raise():
+    from houv_b200 import solver
+    src, tgt, _ = _pairs(0, 1)
+    p = torch.from_numpy(solver.initial_parameters(KERNEL)).cuda()
+    with pytest.raises(RuntimeError):
+        solver.pose_optimise(src.cuda(), tgt.cuda()[:, :200].contiguous(), p, KERNEL, 1)  # N != M
+    with pytest.raises(RuntimeError):
+        solver.pose_optimise(src, tgt, p, KERNEL, 1)  # CPU tensors
+    big = torch.rand(1, 4096, 3).cuda()
+    with pytest.raises(RuntimeError):
+        solver.pose_optimise(big, big, p, KERNEL, 1)  # > 2048 points

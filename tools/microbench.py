@@ -86,5 +86,29 @@ def cmd_chamfer():
                           "GBps": round(byts / med / 1e6, 1)}))
 
 
+def cmd_pose():
+    """K3 at the BASELINE shape: P pairs x 64 starts x `iters` iterations, 2048 points."""
+    import numpy as np
+    from houv_b200 import solver, synth
+    P = int(sys.argv[2]) if len(sys.argv) > 2 else 37
+    iters = int(sys.argv[3]) if len(sys.argv) > 3 else 200
+    s, t, _ = synth.make_pairs(0, P)
+    src, tgt = torch.from_numpy(s).cuda(), torch.from_numpy(t).cuda()
+    init = torch.from_numpy(solver.initial_parameters(P * 64)).cuda()
+    peak = fp32_peak(0)["tflops_best"]
+
+    def run():
+        solver.pose_optimise(src, tgt, init.clone(), 64, iters)
+    med, best = timeit(run, iters=3, warmup=1)
+    evals = 2.0 * 2048 * 2048 * P * 64 * iters  # directed point pairs, each serving 4 metrics
+    print(json.dumps({"kernel": "K3 pose_optimise", "pairs": P, "iters": iters,
+                      "ms": round(med, 2), "pairs_per_s_base0": round(P / med * 1e3, 3),
+                      "us_per_row_iter": round(med * 1e3 / (P * 64 * iters) * 148 * 2, 2),
+                      "tflops_executed_26flop": round(13 * evals / med / 1e9, 2),
+                      "tflops_ref_equiv_64flop": round(32 * evals / med / 1e9, 2),
+                      "frac_fp32_peak_executed": round(13 * evals / med / 1e9 / peak, 3),
+                      "fp32_peak": round(peak, 2)}))
+
+
 if __name__ == "__main__":
-    {"probe": cmd_probe, "chamfer": cmd_chamfer}[sys.argv[1] if len(sys.argv) > 1 else "probe"]()
+    {"probe": cmd_probe, "chamfer": cmd_chamfer, "pose": cmd_pose}[sys.argv[1] if len(sys.argv) > 1 else "probe"]()
