@@ -18,6 +18,7 @@ _SIGNATURES = {
     "houv_nn_search": [_vp, _vp, _ci, _ci, _ci, _vp, _vp, _vp],
     "houv_chamfer3d_backward": [_vp, _vp, _vp, _vp, _vp, _vp, _ci, _ci, _ci, _vp, _vp, _vp],
     "houv_set_nn_variant": [_ci],
+    "houv_set_pose_variant": [_ci],
     "houv_pose_optimise": [_vp, _vp, _ci, _ci, _ci, _ci, _vp, _vp, _vp, _ci, _ci, _ci,
                            _cf, _cf, _cf, _cf, _cf, _cf, _cf, _cf, _vp, _vp, _vp, _vp, _vp, _vp, _vp,
                            _ci, _vp],

@@ -32,8 +32,9 @@ namespace houv {
 
 constexpr int kPts = 2048;       // max points per cloud handled by the fused kernel
 constexpr int kThreads = 256;
-constexpr int kQ = 4;            // queries per thread per scan pass
-constexpr int kG = 8;            // targets per arg-min group
+// Tunables of the scan are template parameters (variants are compiled side by side and
+// picked with houv_set_pose_variant): Q = queries per thread per pass, H = 8-target halves
+// per arg-min group (group = 8*H targets), U = unroll of the group loop.
 constexpr float kInf = __builtin_huge_valf();
 
 struct PoseState;
@@ -95,6 +96,7 @@ __device__ __forceinline__ void block_sum(float (&v)[NV], Smem &S) {
 // One scan pass: kQ queries per thread against `ngroups` groups of 8 targets in
 // SoA shared arrays.  best[m][r], gb[m][r]: running minimum / winning group of
 // metric m (0 = 3-D, 1..3 = view with coordinate m-1 masked) for query r.
+template <int kQ, int H, int U>
 __device__ __forceinline__ void scan_pass(const float *__restrict__ sx, const float *__restrict__ sy,
                                           const float *__restrict__ sz, int ngroups,
                                           const float (&qx)[kQ], const float (&qy)[kQ],
@@ -112,38 +114,54 @@ __device__ __forceinline__ void scan_pass(const float *__restrict__ sx, const fl
 #pragma unroll
         for (int m = 0; m < 4; ++m) { best[m][r] = kInf; gb[m][r] = 0; }
     }
+#pragma unroll U
     for (int g = 0; g < ngroups; ++g) {
-        float4 X[2] = {x4[2 * g], x4[2 * g + 1]};
-        float4 Y[2] = {y4[2 * g], y4[2 * g + 1]};
-        float4 Z[2] = {z4[2 * g], z4[2 * g + 1]};
+        float gm[4][kQ];
 #pragma unroll
-        for (int r = 0; r < kQ; ++r) {
-            float2 f[4], a[4], b[4], c[4];  // full, view0, view1, view2 for the 4 target pairs
+        for (int r = 0; r < kQ; ++r)
 #pragma unroll
-            for (int h = 0; h < 4; ++h) {
-                const float4 &xv = X[h >> 1], &yv = Y[h >> 1], &zv = Z[h >> 1];
-                float2 tx = (h & 1) ? make_float2(xv.z, xv.w) : make_float2(xv.x, xv.y);
-                float2 ty = (h & 1) ? make_float2(yv.z, yv.w) : make_float2(yv.x, yv.y);
-                float2 tz = (h & 1) ? make_float2(zv.z, zv.w) : make_float2(zv.x, zv.y);
-                float2 dx = __fadd2_rn(tx, nqx[r]), dy = __fadd2_rn(ty, nqy[r]),
-                       dz = __fadd2_rn(tz, nqz[r]);
-                float2 yy = __fmul2_rn(dy, dy), xx = __fmul2_rn(dx, dx);
-                float2 xy = __ffma2_rn(dx, dx, yy);
-                f[h] = __ffma2_rn(dz, dz, xy);
-                a[h] = __ffma2_rn(dz, dz, yy);
-                b[h] = __ffma2_rn(dz, dz, xx);
-                c[h] = xy;
-            }
+            for (int m = 0; m < 4; ++m) gm[m][r] = best[m][r];
+#pragma unroll
+        for (int hh = 0; hh < H; ++hh) {
+            const int o = 2 * (g * H + hh);
+            float4 X[2] = {x4[o], x4[o + 1]};
+            float4 Y[2] = {y4[o], y4[o + 1]};
+            float4 Z[2] = {z4[o], z4[o + 1]};
+#pragma unroll
+            for (int r = 0; r < kQ; ++r) {
+                float2 f[4], a[4], b[4], c[4];  // full, view0, view1, view2 of the 4 target pairs
+#pragma unroll
+                for (int h = 0; h < 4; ++h) {
+                    const float4 &xv = X[h >> 1], &yv = Y[h >> 1], &zv = Z[h >> 1];
+                    float2 tx = (h & 1) ? make_float2(xv.z, xv.w) : make_float2(xv.x, xv.y);
+                    float2 ty = (h & 1) ? make_float2(yv.z, yv.w) : make_float2(yv.x, yv.y);
+                    float2 tz = (h & 1) ? make_float2(zv.z, zv.w) : make_float2(zv.x, zv.y);
+                    float2 dx = __fadd2_rn(tx, nqx[r]), dy = __fadd2_rn(ty, nqy[r]),
+                           dz = __fadd2_rn(tz, nqz[r]);
+                    float2 yy = __fmul2_rn(dy, dy), xx = __fmul2_rn(dx, dx);
+                    float2 xy = __ffma2_rn(dx, dx, yy);
+                    f[h] = __ffma2_rn(dz, dz, xy);
+                    a[h] = __ffma2_rn(dz, dz, yy);
+                    b[h] = __ffma2_rn(dz, dz, xx);
+                    c[h] = xy;
+                }
 #define HOUV_FOLD(M, V)                                                              \
     {                                                                                \
-        float gm = min3(min3(V[0].x, V[0].y, V[1].x), V[1].y, V[2].x);               \
-        gm = min3(min3(gm, V[2].y, V[3].x), V[3].y, best[M][r]);                     \
-        gb[M][r] = gm < best[M][r] ? g : gb[M][r];                                   \
-        best[M][r] = gm;                                                             \
+        float t_ = min3(min3(V[0].x, V[0].y, V[1].x), V[1].y, V[2].x);               \
+        gm[M][r] = min3(min3(t_, V[2].y, V[3].x), V[3].y, gm[M][r]);                 \
     }
-            HOUV_FOLD(0, f) HOUV_FOLD(1, a) HOUV_FOLD(2, b) HOUV_FOLD(3, c)
+                HOUV_FOLD(0, f) HOUV_FOLD(1, a) HOUV_FOLD(2, b) HOUV_FOLD(3, c)
 #undef HOUV_FOLD
+            }
         }
+        // strict '<' between groups in ascending order: the first minimum's group wins
+#pragma unroll
+        for (int r = 0; r < kQ; ++r)
+#pragma unroll
+            for (int m = 0; m < 4; ++m) {
+                gb[m][r] = gm[m][r] < best[m][r] ? g : gb[m][r];
+                best[m][r] = gm[m][r];
+            }
     }
 }
 
@@ -258,7 +276,9 @@ __device__ __forceinline__ void adam_step(PoseState &s, const float (&g)[8], con
     }
 }
 
+template <int kQ, int H, int U>
 __global__ void __launch_bounds__(kThreads, 2) pose_kernel(const PoseArgs A) {
+    constexpr int kG = 8 * H;  // targets per arg-min group
     extern __shared__ __align__(16) unsigned char smem_raw[];
     Smem &S = *reinterpret_cast<Smem *>(smem_raw);
     const int t = threadIdx.x;
@@ -339,7 +359,7 @@ __global__ void __launch_bounds__(kThreads, 2) pose_kernel(const PoseArgs A) {
                     q = q < nq ? q : nq - 1;
                     qx[r] = qX[q]; qy[r] = qY[q]; qz[r] = qZ[q];
                 }
-                scan_pass(tX, tY, tZ, ngroups, qx, qy, qz, best, gb);
+                scan_pass<kQ, H, U>(tX, tY, tZ, ngroups, qx, qy, qz, best, gb);
 #pragma unroll
                 for (int r = 0; r < kQ; ++r) {
                     const int q = base + r * kThreads + t;
@@ -532,9 +552,31 @@ __global__ void __launch_bounds__(kThreads, 2) pose_kernel(const PoseArgs A) {
     }
 }
 
+static int g_pose_variant = -1;
+
+template <int kQ, int H, int U>
+static int launch_pose(const PoseArgs &a, cudaStream_t st) {
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(pose_kernel<kQ, H, U>,
+                                             cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             (int)sizeof(Smem));
+        if (e != cudaSuccess) return (int)e;
+        attr_set = true;
+    }
+    pose_kernel<kQ, H, U><<<a.rows, kThreads, sizeof(Smem), st>>>(a);
+    return check_launch();
+}
+
 }  // namespace houv
 
 using namespace houv;
+
+extern "C" int houv_set_pose_variant(int v) {
+    int old = g_pose_variant;
+    g_pose_variant = v;
+    return old;
+}
 
 extern "C" int houv_pose_optimise(const float *src, const float *tgt, int P, int N, int M, int K,
                                   float *params, float *adam_m, float *adam_v, int step0,
@@ -563,13 +605,14 @@ extern "C" int houv_pose_optimise(const float *src, const float *tgt, int P, int
     if (a.k3d < 1 || a.k3d > N) return HOUV_E_BADARG;
     a.lr = lr; a.beta1 = beta1; a.beta2 = beta2; a.eps = eps; a.grad_scale = grad_scale;
     a.w3d = w3d; a.wview = wview;
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(pose_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                             (int)sizeof(Smem));
-        if (e != cudaSuccess) return (int)e;
-        attr_set = true;
+    cudaStream_t st = (cudaStream_t)stream;
+    switch (g_pose_variant) {
+        case 1: return launch_pose<4, 1, 2>(a, st);
+        case 2: return launch_pose<4, 2, 1>(a, st);
+        case 3: return launch_pose<2, 1, 2>(a, st);
+        case 4: return launch_pose<2, 2, 2>(a, st);
+        case 5: return launch_pose<4, 2, 2>(a, st);
+        case 0:
+        default: return launch_pose<4, 1, 1>(a, st);
     }
-    pose_kernel<<<a.rows, kThreads, sizeof(Smem), (cudaStream_t)stream>>>(a);
-    return check_launch();
 }

@@ -93,6 +93,11 @@ int houv_pose_optimise(const float *src, const float *tgt, int P, int N, int M, 
  * (2,128) (4,128) (4,64) (2,256); -1 = built-in default.  Returns the old value. */
 int houv_set_nn_variant(int variant);
 
+/* Tuning knob for the K3 scan shape (queries/thread, 8-target halves per arg-min group,
+ * unroll): 0 (4,1,1) 1 (4,1,2) 2 (4,2,1) 3 (2,1,2) 4 (2,2,2) 5 (4,2,2); -1 = default.
+ * Results are identical for every variant. Returns the old value. */
+int houv_set_pose_variant(int variant);
+
 /* FP32 CUDA-core peak probe: runs `iters` x 64 FFMA (or FFMA2 when packed) per thread on a
  * full-chip grid; *flop_host receives the FLOP it executed (2 per FFMA lane-op).
  * Time it with events around the call to get the roofline denominator. */

@@ -99,6 +99,18 @@ def cmd_pose():
 
     def run():
         solver.pose_optimise(src, tgt, init.clone(), 64, iters)
+    variants = [int(v) for v in sys.argv[4].split(",")] if len(sys.argv) > 4 else [-1]
+    ref = None
+    for v in variants:
+        _lib.load().houv_set_pose_variant(v)
+        p0 = init.clone()
+        o = solver.pose_optimise(src, tgt, p0, 64, 3)
+        same = None if ref is None else bool(torch.equal(ref, p0))
+        ref = p0 if ref is None else ref
+        med, best = timeit(run, iters=3, warmup=1)
+        print(json.dumps({"variant": v, "ms": round(med, 2), "identical_to_first": same,
+                          "pairs_per_s": round(P / med * 1e3, 2)}))
+    _lib.load().houv_set_pose_variant(-1)
     med, best = timeit(run, iters=3, warmup=1)
     evals = 2.0 * 2048 * 2048 * P * 64 * iters  # directed point pairs, each serving 4 metrics
     print(json.dumps({"kernel": "K3 pose_optimise", "pairs": P, "iters": iters,
