@@ -274,7 +274,11 @@ def run_ours(args):
     traffic = None
     tfile = os.path.join(ROOT, "profiles", "k3_traffic.json")
     if os.path.exists(tfile):
-        traffic = json.load(open(tfile)).get("dram_bytes_per_launch")
+        # ncu capture (one launch of 320 rows) scaled to this run's average rows per launch:
+        # the kernel reads each pair's two clouds once per row and nothing else from HBM
+        per_row = json.load(open(tfile)).get("dram_bytes_per_row")
+        if per_row and ktim:
+            traffic = per_row * sum(r for _, _, r, _, _ in ktim) / len(ktim)
     line = {
         "metric": "registered pairs/sec (2048-pt, HOUV full)", "value": value, "unit": "pairs/s",
         "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
