@@ -17,6 +17,9 @@ _SIGNATURES = {
     "houv_chamfer3d_forward": [_vp, _vp, _ci, _ci, _ci, _vp, _vp, _vp, _vp, _vp],
     "houv_nn_search": [_vp, _vp, _ci, _ci, _ci, _vp, _vp, _vp],
     "houv_chamfer3d_backward": [_vp, _vp, _vp, _vp, _vp, _vp, _ci, _ci, _ci, _vp, _vp, _vp],
+    "houv_kabsch": [_vp, _vp, _vp, _ci, _ci, _vp, _vp, _vp],
+    "houv_icp": [_vp, _vp, _ci, _ci, _ci, _vp, _ci, _cf, _ci, ctypes.c_double, ctypes.c_double,
+                 _vp, _vp, _vp],
     "houv_set_nn_variant": [_ci],
     "houv_set_pose_variant": [_ci],
     "houv_pose_optimise": [_vp, _vp, _ci, _ci, _ci, _ci, _vp, _vp, _vp, _ci, _ci, _ci,

@@ -89,6 +89,26 @@ int houv_pose_optimise(const float *src, const float *tgt, int P, int N, int M, 
                        float *trace, const int *row_pair, const int *row_base, int rows,
                        void *stream);
 
+/* Batched Kabsch (K4), SVDHead.forward semantics (model_utils.py:220-255).
+ *   src[B,3,N], src_corr[B,3,N]  channel-first clouds, corresponding columns
+ *   weights[B,N] or NULL         H = (src_c * w) corr_c^T; means stay unweighted (:221-227),
+ *                                t uses the weighted sums (:254)
+ *   R[B,9] row-major, t[B,3]     R = V U^T of H = U S V^T, last column of V negated when
+ *                                det(V U^T) < 0 (:236-239); t = -R mean(src) + mean(corr) */
+int houv_kabsch(const float *src, const float *src_corr, const float *weights, int B, int N,
+                float *R, float *t, void *stream);
+
+/* Point-to-point ICP, one CTA per pair (train_ICP.py:148-151 call site; Open3D 0.9.0
+ * algorithm restated, see csrc/icp.cu).
+ *   src[P,N,3] -> tgt[P,M,3] (N, M <= 2048); init: one row-major 4x4 (init_per_pair = 0) or
+ *   [P,16]; max_distance = correspondence radius (0.02), max_iteration (500),
+ *   relative_fitness / relative_rmse = convergence criteria (Open3D defaults 1e-6).
+ *   T_out[P,16] row-major 4x4 (bottom row 0 0 0 1); stats[P,4] = fitness, inlier_rmse,
+ *   iterations run, number of correspondences of the final evaluation. */
+int houv_icp(const float *src, const float *tgt, int P, int N, int M, const float *init,
+             int init_per_pair, float max_distance, int max_iteration, double relative_fitness,
+             double relative_rmse, float *T_out, float *stats, void *stream);
+
 /* Tuning knob for the NN kernel shape: variant 0..3 = (queries/thread, threads/CTA)
  * (2,128) (4,128) (4,64) (2,256); -1 = built-in default.  Returns the old value. */
 int houv_set_nn_variant(int variant);

@@ -263,3 +263,94 @@ def solve_model(net, src, src_rotated, pose=None, kernel=64, num_epochs=200, pre
     r_err = rotation_error(ans[:, :3, :3], pose[:, :3, :3])
     t_err = translation_error(ans[:, :3, 3], pose[:, :3, 3])
     return r_err, t_err, ans
+
+
+# ---------------------------------------------------------------- Kabsch head
+class SVDHead(nn.Module):
+    """registration/model_utils.py:213-255, restated verbatim in behaviour (per-sample
+    torch.svd loop, reflection fix, weighted translation)."""
+
+    def __init__(self):
+        super().__init__()
+        self.reflect = nn.Parameter(torch.eye(3), requires_grad=False)
+        self.reflect[2, 2] = -1
+
+    def forward(self, src, src_corr, weights=None):
+        src_centered = src - src.mean(dim=2, keepdim=True)
+        src_corr_centered = src_corr - src_corr.mean(dim=2, keepdim=True)
+        if weights is None:
+            H = torch.matmul(src_centered, src_corr_centered.transpose(2, 1).contiguous())
+        else:
+            H = torch.matmul(src_centered * weights, src_corr_centered.transpose(2, 1).contiguous())
+        R = []
+        for i in range(src.size(0)):
+            u, s, v = torch.svd(H[i])
+            r = torch.matmul(v, u.transpose(1, 0).contiguous())
+            if torch.det(r) < 0:
+                u, s, v = torch.svd(H[i])
+                v = torch.matmul(v, self.reflect)
+                r = torch.matmul(v, u.transpose(1, 0).contiguous())
+            R.append(r)
+        R = torch.stack(R, dim=0)
+        if weights is None:
+            t = torch.matmul(-R, src.mean(dim=2, keepdim=True)) + src_corr.mean(dim=2, keepdim=True)
+        else:
+            t = torch.matmul(-R, (weights * src).sum(dim=2, keepdim=True)) + \
+                (weights * src_corr).sum(dim=2, keepdim=True)
+        return R, t.view(src.size(0), 3)
+
+
+# ------------------------------------------------------------------------ ICP
+def icp_point_to_point(source, target, max_distance=0.02, init=None, max_iteration=500,
+                       relative_fitness=1e-6, relative_rmse=1e-6):
+    """PARITY UNPINNED.  float64 restatement of Open3D 0.9.0's
+    registration_icp(..., TransformationEstimationPointToPoint(),
+    ICPConvergenceCriteria(max_iteration)) as called at registration/train_ICP.py:148-151.
+    Open3D (pinned at 0.9.0 by completion/requirements.txt:4) is neither in the reference tree
+    nor installed, and no reference test or fixture exercises it, so this follows the
+    published algorithm:
+        result = evaluate(init)
+        for i < max_iteration: update = umeyama_no_scale(correspondences); T = update @ T;
+                               result' = evaluate(T); stop when both |d fitness| and
+                               |d inlier_rmse| fall below the relative criteria
+        evaluate: nearest target of each transformed source point, a correspondence when the
+                  squared distance < max_distance**2; fitness = #corr/#source,
+                  inlier_rmse = sqrt(sum d^2/#corr)
+    source[N,3], target[M,3] numpy -> (T[4,4] float64, fitness, inlier_rmse, iterations)."""
+    src = np.asarray(source, np.float64)
+    tgt = np.asarray(target, np.float64)
+    T = np.eye(4) if init is None else np.asarray(init, np.float64).copy()
+
+    def evaluate(T):
+        y = src @ T[:3, :3].T + T[:3, 3]
+        d2 = ((y[:, None, :] - tgt[None, :, :]) ** 2).sum(-1)
+        j = d2.argmin(1)
+        d = d2[np.arange(len(y)), j]
+        keep = d < max_distance ** 2
+        n = int(keep.sum())
+        fit = n / float(len(y))
+        rm = float(np.sqrt(d[keep].sum() / n)) if n else 0.0
+        return fit, rm, y[keep], tgt[j[keep]]
+
+    fit, rm, ys, ws = evaluate(T)
+    it = 0
+    for i in range(max_iteration):
+        if len(ys):
+            ym, wm = ys.mean(0), ws.mean(0)
+            H = (ys - ym).T @ (ws - wm)
+            U, S, Vt = np.linalg.svd(H)
+            D = np.eye(3)
+            if np.linalg.det(Vt.T @ U.T) < 0:
+                D[2, 2] = -1
+            R = Vt.T @ D @ U.T
+            upd = np.eye(4)
+            upd[:3, :3] = R
+            upd[:3, 3] = wm - R @ ym
+            T = upd @ T
+        nfit, nrm, ys, ws = evaluate(T)
+        it = i + 1
+        stop = abs(fit - nfit) < relative_fitness and abs(rm - nrm) < relative_rmse
+        fit, rm = nfit, nrm
+        if stop:
+            break
+    return T, fit, rm, it

@@ -22,6 +22,7 @@ import numpy as np
 HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(os.path.dirname(HERE))
 sys.path.insert(0, ROOT)
+sys.path.insert(0, HERE)
 REF = "/root/reference"
 
 
@@ -88,7 +89,70 @@ def make_chamfer():
     print("chamfer fixtures written")
 
 
-FAMILIES = {"chamfer": make_chamfer}
+def make_houv():
+    """houv_ref.npz: outputs of the reference's OWN python files (houv.py,
+    model_utils_completion.py, train_utils.py, loaded unmodified by ref_loader) on small
+    synthetic pairs: reset_weight draws, first-forward loss terms, predict_model after 3
+    iterations at angle_base 0 and 2, solve_model (10 iterations) and the three metrics."""
+    import torch
+    import ref_loader
+    from houv_b200 import synth
+    m = ref_loader.load()
+    H, tu = m["houv"], m["tu"]
+    s, t, tr = synth.make_pairs(100, 2, n_points=128)
+    src, tgt, gt = torch.from_numpy(s), torch.from_numpy(t), torch.from_numpy(tr)
+    out = dict(src=s, tgt=t, transform=tr)
+    net = H.HOUV(64, 0)
+    net.reset_weight(64, 0, seed=2021)
+    for k in ("V_c", "angle_c", "tran_c", "tran_s"):
+        out["init_" + k] = getattr(net, k).detach().numpy().copy()
+    rep = lambda x: x.unsqueeze(1).expand(-1, 32, -1, -1).reshape(-1, 128, 3)
+    src_temp, R, T = net(rep(src))
+    loss, min_1 = H.Predict_loss(src_temp, rep(tgt))
+    out.update(fwd_src_temp=src_temp.detach().numpy(), fwd_R=R.detach().numpy(),
+               fwd_T=T.detach().numpy(), fwd_loss=loss.detach().numpy(),
+               fwd_min_1=min_1.detach().numpy())
+    for base in (0, 2):
+        l, R, T = H.predict_model(H.HOUV(64, 0), src, tgt, kernel=32, num_epochs=3, angle_base=base)
+        out["pm%d_loss" % base] = l.detach().numpy()
+        out["pm%d_R" % base] = R.detach().numpy()
+        out["pm%d_T" % base] = T.detach().numpy()
+    r_err, t_err, ans = H.solve_model(H.HOUV(64, 0), src, tgt, gt, kernel=32, num_epochs=10)
+    out.update(solve_ans=ans.detach().numpy(), solve_r_err=r_err.detach().numpy(),
+               solve_t_err=t_err.detach().numpy(),
+               solve_mse=tu.rmse_loss(src, ans.detach(), gt).numpy())
+    np.savez_compressed(os.path.join(HERE, "houv_ref.npz"), **out)
+    print("houv fixtures written")
+
+
+def make_svd():
+    """svdhead_ref.npz: the reference's SVDHead class (model_utils.py:213-255, source read
+    and executed as-is) on noisy rigid correspondences, with and without weights, including
+    a mirrored sample that exercises the det<0 branch."""
+    import torch
+    import ref_loader
+
+    class Args:
+        use_fpfh = False
+        descriptor_size = 8
+    head = ref_loader.load_svdhead()(Args())
+    torch.manual_seed(11)
+    B, N = 6, 200
+    src = torch.randn(B, 3, N) * 0.3
+    Rg = torch.linalg.qr(torch.randn(B, 3, 3))[0]
+    Rg = Rg * torch.sign(torch.det(Rg)).reshape(B, 1, 1)
+    corr = Rg @ src + torch.randn(B, 3, 1) * 0.2 + 0.005 * torch.randn(B, 3, N)
+    corr[5] = corr[5] * torch.tensor([1.0, 1.0, -1.0]).reshape(3, 1)  # reflection -> det fix
+    w = torch.rand(B, 1, N)
+    R0, t0 = head(src, corr)
+    R1, t1 = head(src, corr, w)
+    np.savez_compressed(os.path.join(HERE, "svdhead_ref.npz"), src=src.numpy(), corr=corr.numpy(),
+                        weights=w.numpy(), R=R0.numpy(), t=t0.numpy(), Rw=R1.numpy(),
+                        tw=t1.numpy())
+    print("svd fixtures written")
+
+
+FAMILIES = {"chamfer": make_chamfer, "houv": make_houv, "svd": make_svd}
 
 if __name__ == "__main__":
     want = sys.argv[1:] or list(FAMILIES)

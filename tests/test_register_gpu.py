@@ -1,0 +1,180 @@
+"""GPU: the registration calls above the kernels -- solve_model (houv.py:142-206),
+SVDHead (model_utils.py:213-255) and the ICP block of train_ICP.py:124-190 -- through the
+drop-in Python surface, against the oracle and the reference-made golden vectors."""
+import numpy as np
+import pytest
+import torch
+
+from houv_b200 import synth
+from oracle import houv as oh
+from tests.util import load_npz
+
+pytestmark = pytest.mark.gpu
+
+
+def _geodesic_rad(Ra, Rb):
+    c = (np.einsum("bij,bij->b", Ra, Rb) - 1) / 2
+    return np.arccos(np.clip(c, -1, 1))
+
+
+# ------------------------------------------------------------------ solve_model
+def test_predict_model_matches_reference_golden():
+    """3 iterations, reference-made fixture (houv.py run unmodified in the dev container)."""
+    from houv_b200 import solver
+    g = load_npz("houv_ref.npz")
+    src, tgt = torch.from_numpy(g["src"]).cuda(), torch.from_numpy(g["tgt"]).cuda()
+    for base in (0, 2):
+        net = solver.HOUV(64, 0)
+        l, R, T = solver.predict_model(net, src, tgt, kernel=32, num_epochs=3, angle_base=base)
+        assert l.shape == (2, 32) and R.shape == (2, 32, 3, 3) and T.shape == (2, 32, 3)
+        ref = g["pm%d_loss" % base]
+        assert np.abs(l.cpu().numpy() - ref).max() < 2e-5 * np.abs(ref).max()
+        assert np.abs(R.cpu().numpy() - g["pm%d_R" % base]).max() < 2e-5
+        assert np.abs(T.cpu().numpy() - g["pm%d_T" % base]).max() < 2e-5
+        assert net.V_c.shape == (64, 3) and net.V_c.is_cuda  # net holds the stepped parameters
+
+
+def test_solve_model_matches_reference_golden():
+    """solve_model, 10 iterations incl. the angle_base 1..3 retries, reference-made fixture.
+    north_star end-state bar on the selected start: rotation 1e-4 rad, translation 1e-5."""
+    from houv_b200 import solver
+    g = load_npz("houv_ref.npz")
+    src, tgt, gt = (torch.from_numpy(g[k]).cuda() for k in ("src", "tgt", "transform"))
+    r_err, t_err, ans = solver.solve_model(solver.HOUV(64, 0), src, tgt, gt, kernel=32,
+                                           num_epochs=10)
+    a = ans.cpu().numpy()
+    assert np.abs(a[:, 3]).max() == 0  # zero bottom row like the reference
+    assert _geodesic_rad(a[:, :3, :3], g["solve_ans"][:, :3, :3]).max() < 1e-4
+    assert np.abs(a[:, :3, 3] - g["solve_ans"][:, :3, 3]).max() < 1e-5
+    assert np.abs(r_err.cpu().numpy() - g["solve_r_err"]).max() < 1e-2  # degrees
+    assert np.abs(t_err.cpu().numpy() - g["solve_t_err"]).max() < 1e-5
+    cpu = solver.solve_model(solver.HOUV(64, 0), src, tgt, None, kernel=32, num_epochs=10,
+                             prefix='test')
+    assert not cpu.is_cuda and torch.equal(cpu, ans.cpu())  # houv.py:199-200
+
+
+def test_solve_model_vs_oracle_with_retries():
+    """Pairs chosen so that some stay above 0.030 and take the retry path; the fused single
+    launch of the three retries must reproduce the oracle's sequential keep-if-better."""
+    from houv_b200 import solver
+    s, t, tr = synth.make_pairs(40, 4, n_points=192)
+    src, tgt, gt = torch.from_numpy(s), torch.from_numpy(t), torch.from_numpy(tr)
+    r0, t0, a0 = oh.solve_model(oh.HOUV(), src, tgt, gt, kernel=32, num_epochs=8)
+    r1, t1, a1 = solver.solve_model(solver.HOUV(128, 0), src.cuda(), tgt.cuda(), gt.cuda(),
+                                    kernel=32, num_epochs=8)
+    a0, a1 = a0.numpy(), a1.cpu().numpy()
+    assert _geodesic_rad(a0[:, :3, :3], a1[:, :3, :3]).max() < 1e-4
+    assert np.abs(a0[:, :3, 3] - a1[:, :3, 3]).max() < 1e-5
+
+
+def test_full_size_properties():
+    """2048 points, 64 starts (BASELINE shape), short horizon: properties that need no oracle --
+    R orthonormal with det +1, |T| inside the 0..0.25 window of houv.py:99, min_1 equals the
+    unfused operator path on the returned pose, loss non-increasing on average."""
+    from houv_b200 import solver
+    from houv_b200.loss import calc_cd_percent
+    s, t, _ = synth.make_pairs(0, 3)
+    src, tgt = torch.from_numpy(s).cuda(), torch.from_numpy(t).cuda()
+    params = torch.from_numpy(solver.initial_parameters(3 * 64)).cuda()
+    out = solver.pose_optimise(src, tgt, params, 64, 12, want_trace=True)
+    R, T = out["R"], out["T"]
+    eye = torch.eye(3, device="cuda").expand_as(R)
+    assert (R @ R.transpose(1, 2) - eye).abs().max() < 1e-5
+    assert (torch.det(R) - 1).abs().max() < 1e-5
+    assert T.norm(dim=1).max() <= 0.25 + 1e-6
+    moved = src.repeat_interleave(64, 0) @ R.transpose(1, 2) + T.unsqueeze(1)
+    cd_p, cd_t = calc_cd_percent(moved, tgt.repeat_interleave(64, 0), percent=0.5)
+    ref = torch.minimum(cd_p, cd_t)
+    assert ((out["min_1"] - ref).abs() / ref).max() < 1e-5
+    tr = out["trace"][:, :, 0].mean(1)
+    assert tr[-1] < tr[0]
+
+
+# ---------------------------------------------------------------------- SVDHead
+def test_svdhead_matches_reference_golden():
+    from houv_b200.kabsch import SVDHead
+    g = load_npz("svdhead_ref.npz")
+    src, corr, w = (torch.from_numpy(g[k]).cuda() for k in ("src", "corr", "weights"))
+    head = SVDHead(None)
+    R, t = head(src, corr)
+    assert R.shape == (6, 3, 3) and t.shape == (6, 3)
+    assert np.abs(R.cpu().numpy() - g["R"]).max() < 1e-5
+    assert np.abs(t.cpu().numpy() - g["t"]).max() < 1e-5
+    Rw, tw = head(src, corr, w)
+    assert np.abs(Rw.cpu().numpy() - g["Rw"]).max() < 1e-5
+    assert np.abs(tw.cpu().numpy() - g["tw"]).max() < 1e-5
+    assert (torch.det(R) - 1).abs().max() < 1e-5
+
+
+@pytest.mark.parametrize("B,N", [(1, 3), (7, 33), (1200, 2048)])
+def test_svdhead_vs_oracle_random(B, N):
+    from houv_b200.kabsch import kabsch
+    torch.manual_seed(B)
+    src = torch.randn(B, 3, N) * 0.3
+    Rg = torch.linalg.qr(torch.randn(B, 3, 3))[0]
+    corr = Rg @ src + torch.randn(B, 3, 1) * 0.1 + 0.01 * torch.randn(B, 3, N)
+    n_ref = min(B, 40)  # the oracle loops per sample like the reference
+    Ro, to = oh.SVDHead()(src[:n_ref], corr[:n_ref])
+    R, t = kabsch(src.cuda(), corr.cuda())
+    assert (R[:n_ref].cpu() - Ro).abs().max() < 2e-5 and (t[:n_ref].cpu() - to).abs().max() < 2e-5
+    eye = torch.eye(3, device="cuda").expand_as(R)
+    assert (R @ R.transpose(1, 2) - eye).abs().max() < 1e-5 and (torch.det(R) - 1).abs().max() < 1e-5
+
+
+def test_svdhead_degenerate_inputs():
+    from houv_b200.kabsch import kabsch
+    z = torch.zeros(2, 3, 10).cuda()
+    R, t = kabsch(z, z)  # H = 0: any rotation is optimal; must still be a rotation
+    assert torch.isfinite(R).all() and (torch.det(R) - 1).abs().max() < 1e-5
+    line = torch.zeros(1, 3, 10).cuda()
+    line[0, 0] = torch.arange(10.0)
+    R, t = kabsch(line, line)  # rank-1 H
+    assert torch.isfinite(R).all() and (torch.det(R) - 1).abs().max() < 1e-5
+    assert ((R @ line + t.unsqueeze(-1)) - line).abs().max() < 1e-4
+
+
+# -------------------------------------------------------------------------- ICP
+def test_icp_vs_float64_oracle():
+    from houv_b200.icp import TRANS_INIT, registration_icp
+    rng = np.random.RandomState(3)
+    P, N = 4, 500
+    tgt = (rng.rand(P, N, 3) - 0.5).astype(np.float32)
+    src = np.empty_like(tgt)
+    inits = []
+    for p in range(P):
+        Rp, _ = synth.random_rotation(rng, np.deg2rad(4.0))
+        tp = rng.randn(3) * 0.004
+        src[p] = ((tgt[p] - tp) @ Rp).astype(np.float32)  # tgt = Rp src + tp
+        inits.append(np.eye(4))
+    reg = registration_icp(torch.from_numpy(src).cuda(), torch.from_numpy(tgt).cuda(), 0.05,
+                           np.eye(4, dtype=np.float32), 200)
+    T = reg.transformation.cpu().numpy()
+    for p in range(P):
+        To, fit, rm, it = oh.icp_point_to_point(src[p], tgt[p], 0.05, np.eye(4), 200)
+        assert _geodesic_rad(T[p:p + 1, :3, :3], To[None, :3, :3]).max() < 1e-4
+        assert np.abs(T[p, :3, 3] - To[:3, 3]).max() < 1e-5
+        assert abs(float(reg.fitness[p]) - fit) < 1e-6
+        assert abs(float(reg.inlier_rmse[p]) - rm) < 1e-5
+    assert np.allclose(T[:, 3], [0, 0, 0, 1])
+    # the train_ICP call shape: fixed initial rotation, threshold 0.02, 500 iterations
+    reg2 = registration_icp(torch.from_numpy(src).cuda(), torch.from_numpy(tgt).cuda(), 0.02,
+                            TRANS_INIT, 500)
+    assert reg2.transformation.shape == (P, 4, 4) and torch.isfinite(reg2.transformation).all()
+
+
+def test_icp_no_correspondences_keeps_init():
+    from houv_b200.icp import registration_icp
+    src = torch.rand(2, 64, 3).cuda()
+    tgt = src + 10.0
+    reg = registration_icp(src, tgt, 0.02, np.eye(4, dtype=np.float32), 50)
+    assert torch.equal(reg.transformation.cpu(), torch.eye(4).expand(2, 4, 4))
+    assert float(reg.fitness.max()) == 0 and float(reg.correspondences.max()) == 0
+
+
+def test_icp_batch_metrics_shape():
+    from houv_b200.icp import icp_batch
+    s, t, tr = synth.make_pairs(0, 5, n_points=512)
+    ans, r_err, t_err, mse = icp_batch(torch.from_numpy(s).cuda(), torch.from_numpy(t).cuda(),
+                                       torch.from_numpy(tr).cuda())
+    assert ans.shape == (5, 4, 4) and r_err.shape == (5,) and t_err.shape == (5,) and mse.shape == (5,)
+    assert torch.isfinite(ans).all()
