@@ -13,8 +13,12 @@ pytestmark = pytest.mark.gpu
 
 
 def _geodesic_rad(Ra, Rb):
-    c = (np.einsum("bij,bij->b", Ra, Rb) - 1) / 2
-    return np.arccos(np.clip(c, -1, 1))
+    """angle of Ra^T Rb from its skew part (acos of the trace loses ~3e-4 rad in float32)"""
+    M = np.einsum("bji,bjk->bik", Ra.astype(np.float64), Rb.astype(np.float64))
+    v = 0.5 * np.stack([M[:, 2, 1] - M[:, 1, 2], M[:, 0, 2] - M[:, 2, 0], M[:, 1, 0] - M[:, 0, 1]], 1)
+    s = np.linalg.norm(v, axis=1)
+    c = (np.trace(M, axis1=1, axis2=2) - 1) / 2
+    return np.arctan2(s, c)
 
 
 # ------------------------------------------------------------------ solve_model
