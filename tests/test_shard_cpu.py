@@ -1,0 +1,87 @@
+"""CPU: host logic of the multi-GPU driver with a world_size-2 gloo group -- contiguous
+range sharding (test_mult.py -l/-r semantics), per-batch solve calls, and the ONE all-gather
+of poses + metrics.  The GPU solve is replaced by a deterministic stand-in (no compute calls
+without a GPU); the real path is covered by bench.py --gpus N on the box."""
+import os
+import socket
+
+import numpy as np
+import torch
+import torch.multiprocessing as mp
+
+from houv_b200 import shard
+
+
+def test_shard_ranges_cover_and_are_contiguous():
+    for total, world in [(1200, 8), (1200, 1), (10, 4), (3, 8), (0, 2)]:
+        seen = []
+        for r in range(world):
+            l, rr = shard.shard_range(total, r, world)
+            assert 0 <= l <= rr <= total
+            seen += list(range(l, rr))
+        assert seen == list(range(total))
+    assert shard.shard_range(1200, 3, 8) == (450, 600)
+
+
+def _fake_solve(net, src, tgt, pose, kernel=64, num_epochs=200, prefix='device'):
+    # pose that depends only on the pair's data: rank/batch layout must not matter
+    ans = torch.zeros(src.shape[0], 4, 4)
+    ans[:, :3, :3] = torch.eye(3)
+    ans[:, :3, 3] = tgt.mean(1) - src.mean(1)
+    return ans
+
+
+class _NoNet:
+    def __init__(self, *a, **k):
+        pass
+
+
+def _worker(rank, world, port, total, batch, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank),
+                      WORLD_SIZE=str(world), LOCAL_RANK=str(rank))
+    r, w, _ = shard.init_distributed("gloo")
+    assert (r, w) == (rank, world)
+    rng = np.random.RandomState(0)
+    src = torch.from_numpy(rng.rand(total, 16, 3).astype(np.float32))
+    tgt = torch.from_numpy(rng.rand(total, 16, 3).astype(np.float32))
+    gt = torch.eye(4).repeat(total, 1, 1)
+    l, rr = shard.shard_range(total, rank, world)
+    shard.solver.HOUV = _NoNet
+    ans, met = shard.register_pairs(src[l:rr], tgt[l:rr], gt[l:rr], batch_size=batch, kernel=4,
+                                    num_epochs=1, solve=_fake_solve)
+    ans_all, met_all = shard.gather_results(ans, met, world)
+    q.put((rank, ans_all.numpy(), met_all.numpy()))
+    torch.distributed.barrier()
+    torch.distributed.destroy_process_group()
+
+
+def test_gloo_world2_gather_matches_single_process():
+    total, batch, world = 12, 3, 2
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_worker, args=(r, world, port, total, batch, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    got = [q.get(timeout=120) for _ in range(world)]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    # single-process reference of the same computation
+    rng = np.random.RandomState(0)
+    src = torch.from_numpy(rng.rand(total, 16, 3).astype(np.float32))
+    tgt = torch.from_numpy(rng.rand(total, 16, 3).astype(np.float32))
+    gt = torch.eye(4).repeat(total, 1, 1)
+    real = shard.solver.HOUV
+    shard.solver.HOUV = _NoNet
+    try:
+        ans, met = shard.register_pairs(src, tgt, gt, batch_size=batch, kernel=4, num_epochs=1,
+                                        solve=_fake_solve)
+    finally:
+        shard.solver.HOUV = real
+    for rank, a, m in got:
+        assert a.shape == (total, 4, 4) and m.shape == (total, 3)
+        assert np.array_equal(a, ans.numpy()) and np.allclose(m, met.numpy())
