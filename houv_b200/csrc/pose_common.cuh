@@ -1,0 +1,144 @@
+// Shared pieces of the K3 pose-optimisation kernels (pose_opt.cu: two directed scans per
+// iteration; pose_sym.cu: one symmetric scan serving both directions).
+#pragma once
+#include "common.cuh"
+
+namespace houv {
+
+constexpr int kPts = 2048;       // max points per cloud handled by the fused kernel
+constexpr int kThreads = 256;
+constexpr float kInf = __builtin_huge_valf();
+
+struct PoseState;
+struct PoseArgs {
+    const float *src;   // [P,N,3]
+    const float *tgt;   // [P,M,3]
+    float *params;      // [rows,8] in/out: V_c[3], angle_c, tran_c[3], tran_s
+    float *adam_m;      // [rows,8] in/out or null
+    float *adam_v;      // [rows,8] in/out or null
+    float *min1_out;    // [rows]   3-D trimmed term of the LAST forward
+    float *loss_out;    // [rows]   6*min_1 + sum of view terms of the last forward (or null)
+    float *R_out;       // [rows,9]
+    float *T_out;       // [rows,3]
+    float *trace;       // [iters,rows,2] (loss, min_1) per forward, or null
+    const int *row_pair;  // [rows] pair of each row, or null (= row / K)
+    const int *row_base;  // [rows] angle_base of each row, or null (= angle_base)
+    int P, N, M, K, rows;
+    int step0, iters, angle_base, k3d;
+    float lr, beta1, beta2, eps, grad_scale, w3d, wview;
+};
+
+// squared distance of metric m between (tx,ty,tz) and (qx,qy,qz), scalar, same
+// arithmetic as the packed scan (and as the reference on masked clouds)
+__device__ __forceinline__ float metric_dist(int m, float tx, float ty, float tz, float qx,
+                                             float qy, float qz) {
+    float dx = __fsub_rn(tx, qx), dy = __fsub_rn(ty, qy), dz = __fsub_rn(tz, qz);
+    float yy = __fmul_rn(dy, dy);
+    if (m == 0) return __fmaf_rn(dz, dz, __fmaf_rn(dx, dx, yy));
+    if (m == 1) return __fmaf_rn(dz, dz, yy);
+    if (m == 2) return __fmaf_rn(dz, dz, __fmul_rn(dx, dx));
+    return __fmaf_rn(dx, dx, yy);
+}
+
+// Per-row optimiser state, live in thread 0's registers for the whole kernel.
+struct PoseState {
+    float p[8], m[8], v[8];
+    // forward intermediates kept for the closed-form backward
+    float vh[3], n, A[3][3], A2[3][3], sa, ca, ang, u[3], nt, st;
+};
+
+__device__ __forceinline__ void pose_forward(PoseState &s, float boff, float *pose /*smem[12]*/) {
+    const float pi = 3.14159274101257324f;  // float32 pi = acos(0)*2, houv.py:19
+    // angle = sin(angle_c*pi)*pi/8 + pi/8 + angle_base*pi/4            houv.py:96
+    s.ang = __fadd_rn(__fadd_rn(__fmul_rn(sinf(__fmul_rn(s.p[3], pi)), pi) / 8.f, pi / 8.f), boff);
+    // V / sqrt(sum V^2)                                                 houv.py:71
+    s.n = sqrtf(__fadd_rn(__fadd_rn(__fmul_rn(s.p[0], s.p[0]), __fmul_rn(s.p[1], s.p[1])),
+                          __fmul_rn(s.p[2], s.p[2])));
+#pragma unroll
+    for (int i = 0; i < 3; ++i) s.vh[i] = s.p[i] / s.n;
+    float (&A)[3][3] = s.A;
+    A[0][0] = 0.f; A[0][1] = -s.vh[2]; A[0][2] = s.vh[1];
+    A[1][0] = s.vh[2]; A[1][1] = 0.f; A[1][2] = -s.vh[0];
+    A[2][0] = -s.vh[1]; A[2][1] = s.vh[0]; A[2][2] = 0.f;
+#pragma unroll
+    for (int i = 0; i < 3; ++i)
+#pragma unroll
+        for (int j = 0; j < 3; ++j)
+            s.A2[i][j] = __fmaf_rn(A[i][2], A[2][j], __fmaf_rn(A[i][1], A[1][j], __fmul_rn(A[i][0], A[0][j])));
+    s.sa = sinf(s.ang);
+    s.ca = cosf(s.ang);
+    const float omc = __fsub_rn(1.f, s.ca);
+    // R = I + sin(a) A + (1-cos a) A^2                                   houv.py:85
+#pragma unroll
+    for (int i = 0; i < 3; ++i)
+#pragma unroll
+        for (int j = 0; j < 3; ++j)
+            pose[i * 3 + j] = __fadd_rn(__fadd_rn(i == j ? 1.f : 0.f, __fmul_rn(s.sa, A[i][j])),
+                                        __fmul_rn(omc, s.A2[i][j]));
+    // T = tran_c/|tran_c| * (sin(tran_s*pi)*0.125 + 0.125)               houv.py:88-100
+    s.st = __fadd_rn(__fmul_rn(sinf(__fmul_rn(s.p[7], pi)), 0.125f), 0.125f);
+    s.nt = sqrtf(__fadd_rn(__fadd_rn(__fmul_rn(s.p[4], s.p[4]), __fmul_rn(s.p[5], s.p[5])),
+                           __fmul_rn(s.p[6], s.p[6])));
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+        s.u[i] = s.p[4 + i] / s.nt;
+        pose[9 + i] = __fmul_rn(s.u[i], s.st);
+    }
+}
+
+// Closed-form chain from dL/dR (GR), dL/dT (gT) to the 8 scalars.
+__device__ __forceinline__ void pose_backward(const PoseState &s, const float (&GR)[3][3],
+                                              const float (&gT)[3], float (&g)[8]) {
+    const float pi = 3.14159274101257324f;
+    float dA = 0.f, dA2 = 0.f;
+#pragma unroll
+    for (int i = 0; i < 3; ++i)
+#pragma unroll
+        for (int j = 0; j < 3; ++j) {
+            dA += GR[i][j] * s.A[i][j];
+            dA2 += GR[i][j] * s.A2[i][j];
+        }
+    const float dang = s.ca * dA + s.sa * dA2;  // d/da [sin a A + (1-cos a) A^2]
+    const float omc = 1.f - s.ca;
+    float GA[3][3];  // dL/dA = sin(a) GR + (1-cos a)(GR A^T + A^T GR)
+#pragma unroll
+    for (int i = 0; i < 3; ++i)
+#pragma unroll
+        for (int j = 0; j < 3; ++j) {
+            float t = 0.f;
+#pragma unroll
+            for (int k = 0; k < 3; ++k) t += GR[i][k] * s.A[j][k] + s.A[k][i] * GR[k][j];
+            GA[i][j] = s.sa * GR[i][j] + omc * t;
+        }
+    const float gv[3] = {GA[2][1] - GA[1][2], GA[0][2] - GA[2][0], GA[1][0] - GA[0][1]};
+    const float vdot = s.vh[0] * gv[0] + s.vh[1] * gv[1] + s.vh[2] * gv[2];
+#pragma unroll
+    for (int i = 0; i < 3; ++i) g[i] = (gv[i] - s.vh[i] * vdot) / s.n;
+    g[3] = dang * (pi / 8.f) * cosf(s.p[3] * pi) * pi;
+    const float gs = gT[0] * s.u[0] + gT[1] * s.u[1] + gT[2] * s.u[2];
+    const float udot = gs * s.st;  // u . (gT * st)
+#pragma unroll
+    for (int i = 0; i < 3; ++i) g[4 + i] = (gT[i] * s.st - s.u[i] * udot) / s.nt;
+    g[7] = gs * 0.125f * cosf(s.p[7] * pi) * pi;
+}
+
+// torch.optim.Adam, default betas/eps, no weight decay / amsgrad (houv.py:118)
+__device__ __forceinline__ void adam_step(PoseState &s, const float (&g)[8], const PoseArgs &A,
+                                          double &b1t, double &b2t) {
+    b1t *= (double)A.beta1;
+    b2t *= (double)A.beta2;
+    const float step_size = (float)((double)A.lr / (1.0 - b1t));
+    const float bc2_sqrt = (float)sqrt(1.0 - b2t);
+    const float omb1 = (float)(1.0 - (double)A.beta1), omb2 = (float)(1.0 - (double)A.beta2);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        s.m[i] = __fadd_rn(__fmul_rn(s.m[i], A.beta1), __fmul_rn(omb1, g[i]));
+        s.v[i] = __fadd_rn(__fmul_rn(s.v[i], A.beta2), __fmul_rn(omb2, __fmul_rn(g[i], g[i])));
+        const float denom = __fadd_rn(sqrtf(s.v[i]) / bc2_sqrt, A.eps);
+        s.p[i] = __fsub_rn(s.p[i], __fmul_rn(step_size, s.m[i] / denom));
+    }
+}
+
+int launch_pose_sym(const PoseArgs &a, cudaStream_t st);  // pose_sym.cu
+
+}  // namespace houv

@@ -1,0 +1,501 @@
+// K3 (symmetric scan) -- fused HOUV pose optimisation for sm_100a, one CTA of 512 threads
+// keeps one start (row of the multi-start batch) resident for ALL iterations, one CTA per SM.
+//
+// Same contract and same per-iteration semantics as pose_opt.cu (predict_model's hot loop,
+// /root/reference/registration/models/houv.py:120-126: HOUV.forward :94-103, Predict_loss
+// :209-222 = 4 x chamfer_3DDist forward [chamfer3D.cu:12-154] + top-k trimmed sqrt-means
+// [model_utils_completion.py:83-100], autograd backward [chamfer3D.cu:155-195], Adam :118).
+//
+// What is different: the reference's two directed searches of one Chamfer call evaluate the SAME
+// N x M matrix -- d(i,j) of "src_i queries tgt_j" is (t-y)^2 summed and of "tgt_j queries src_i"
+// is (y-t)^2 summed in the same order, and fl(a-b) == -fl(b-a), so both are bit-identical.
+// This kernel evaluates every d(i,j) ONCE (9 packed lane-ops for the four metrics) and folds
+// it into a row minimum (src_i's nearest tgt) and a column minimum (tgt_j's nearest src):
+//
+//  * a thread owns 8 source rows in registers for the whole sweep; target columns stream past
+//    the lanes in a rotation: in every step a lane evaluates its 8 rows against ONE pair of
+//    columns (FADD2/FMUL2/FFMA2, the two columns are the two packed halves), and the running
+//    column minima of that pair travel with it from lane to lane (8 SHFL per 16 evaluations);
+//    the rotation runs inside 8-lane groups, so a finished column minimum covers 64 rows;
+//  * row minima: one FMNMX3 per metric and row per step; column minima: FMNMX3 over row pairs.
+//    Issue cost 72 packed + 64 FMNMX3 + 8 SHFL + 3 LDS.64 per 16 evaluations (~9.4 slots per
+//    evaluation against 2 x 8.9 in the two-scan kernel);
+//  * arg-min bookkeeping is by 64-wide groups, exact index recovered later only where the
+//    gradient needs it: rows remember the 64-column superblock that last strictly improved
+//    them (checked once per superblock against a shadow copy in shared memory); columns get
+//    the FIRST 64-row sub-group (ascending, strict '<') holding their minimum from a per-
+//    superblock reduction of the sub-groups' partial minima.  Ascending order + strict '<' at
+//    every level = the reference's first-minimum rule (chamfer3D.cu:36,46,126);
+//  * threads 0..255 sweep the lower half of the superblocks, threads 256..511 the upper half
+//    with the same rows; the two row results are merged with the lower half winning ties.
+//
+// Everything after the scan (radix select of the k-th smallest, the min() side selection,
+// gradient through the winning side, closed-form pose backward, Adam) is as in pose_opt.cu.
+#include "pose_common.cuh"
+
+namespace houv {
+
+constexpr int kSymThreads = 512;
+constexpr int kSB = 64;        // columns per superblock = rows per sub-group = arg-min group width
+constexpr int kRowsPerThread = 8;
+
+struct SmemSym {
+    float tx[kPts], ty[kPts], tz[kPts];   // target cloud (columns), fixed
+    float yx[kPts], yy[kPts], yz[kPts];   // transformed source (rows) of this iteration
+    float d3[2][kPts];                    // 3-D metric: [0] = column minima (dist1), [1] = row minima (dist2)
+    unsigned char gid[4][2][kPts];        // winning group: [m][0][col] = 64-row sub-group, [m][1][row] = superblock
+    unsigned char rgid1[4][kPts];         // rows: winning superblock seen by the upper column half
+    float part[2][32][4][kSB];            // [column half][sub-group][metric][column]: partial column minima
+    float shadow[32][kSymThreads];        // row minima as of the last superblock boundary, [metric*8+r][thread]
+    int hist[2][256];
+    float red[kSymThreads / 32][16];
+    float pose[12];
+    unsigned selu[8];
+    float state[96];
+    double bt[2];
+};
+
+template <int NV>
+__device__ __forceinline__ void block_sum_sym(float (&v)[NV], SmemSym &S) {
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) v[i] += __shfl_xor_sync(0xffffffffu, v[i], o);
+    }
+    const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+    __syncthreads();
+    if (l == 0) {
+#pragma unroll
+        for (int i = 0; i < NV; ++i) S.red[w][i] = v[i];
+    }
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+        float s = 0.f;
+#pragma unroll
+        for (int ww = 0; ww < kSymThreads / 32; ++ww) s += S.red[ww][i];
+        v[i] = s;
+    }
+}
+
+// The four metrics of one (row, column pair): f = 3-D, a/b/c = view with x/y/z masked.
+// Same contraction as the reference on (masked) clouds: yy=dy*dy; xy=fma(dx,dx,yy);
+// f=fma(dz,dz,xy); a=fma(dz,dz,yy); b=fma(dz,dz,dx*dx); c=xy.
+__device__ __forceinline__ void eval4(const float2 X, const float2 Y, const float2 Z, float nqx,
+                                      float nqy, float nqz, float2 &f, float2 &a, float2 &b,
+                                      float2 &c) {
+    const float2 dx = __fadd2_rn(X, make_float2(nqx, nqx));
+    const float2 dy = __fadd2_rn(Y, make_float2(nqy, nqy));
+    const float2 dz = __fadd2_rn(Z, make_float2(nqz, nqz));
+    const float2 yy = __fmul2_rn(dy, dy), xx = __fmul2_rn(dx, dx);
+    c = __ffma2_rn(dx, dx, yy);
+    f = __ffma2_rn(dz, dz, c);
+    a = __ffma2_rn(dz, dz, yy);
+    b = __ffma2_rn(dz, dz, xx);
+}
+
+// One rotation step: 8 rows x one column pair.
+__device__ __forceinline__ void sym_step(const float2 X, const float2 Y, const float2 Z,
+                                         const float (&nqx)[8], const float (&nqy)[8],
+                                         const float (&nqz)[8], float (&best)[4][8],
+                                         float2 (&cm)[4]) {
+#pragma unroll
+    for (int r = 0; r < 8; r += 2) {
+        float2 v0[4], v1[4];
+        eval4(X, Y, Z, nqx[r], nqy[r], nqz[r], v0[0], v0[1], v0[2], v0[3]);
+        eval4(X, Y, Z, nqx[r + 1], nqy[r + 1], nqz[r + 1], v1[0], v1[1], v1[2], v1[3]);
+#pragma unroll
+        for (int m = 0; m < 4; ++m) {
+            best[m][r] = min3(best[m][r], v0[m].x, v0[m].y);
+            best[m][r + 1] = min3(best[m][r + 1], v1[m].x, v1[m].y);
+            cm[m].x = min3(cm[m].x, v0[m].x, v1[m].x);
+            cm[m].y = min3(cm[m].y, v0[m].y, v1[m].y);
+        }
+    }
+}
+
+__global__ void __launch_bounds__(kSymThreads, 1) pose_sym_kernel(const PoseArgs A) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    SmemSym &S = *reinterpret_cast<SmemSym *>(smem_raw);
+    const int t = threadIdx.x;
+    const int row = blockIdx.x;
+    const int pair = A.row_pair ? A.row_pair[row] : row / A.K;
+    const int N = A.N, M = A.M;  // rows = source points, columns = target points
+    const float *src = A.src + (size_t)pair * N * 3;
+    const float *tgt = A.tgt + (size_t)pair * M * 3;
+
+    // geometry of the sweep
+    const int half = t >> 8;            // which half of the superblocks this thread sweeps
+    const int u = t & 255;              // thread within the half: owns rows 8u .. 8u+7
+    const int w = u >> 5, l = u & 31;   // warp within the half, lane
+    const int gq = l >> 3, ll = l & 7;  // 8-lane rotation group, lane within it
+    const int sg = w * 4 + gq;          // 64-row sub-group: rows 64*sg .. 64*sg+63
+    const int nsb = (M + kSB - 1) / kSB;          // superblocks holding real columns
+    const int nsbh = (nsb + 1) / 2;               // rounds: superblocks per half
+    const int nsg = (N + kSB - 1) / kSB;          // sub-groups holding real rows
+    const bool scan_active = 256 * w < N;         // warp-uniform: this warp owns real rows
+    const int row0 = 8 * u;
+    int pad = 2 * nsbh * kSB;                     // columns touched by the sweep
+    const int rpad = (N + 255) / 256 * 256;       // rows touched by the sweep
+    pad = pad > rpad ? pad : rpad;                // (<= kPts)
+
+    // target cloud -> shared SoA, +inf padded in x and y so every metric of a padded point is inf
+    for (int j = t; j < pad; j += kSymThreads) {
+        const bool ok = j < M;
+        S.tx[j] = ok ? __ldg(tgt + 3 * j + 0) : kInf;
+        S.ty[j] = ok ? __ldg(tgt + 3 * j + 1) : kInf;
+        S.tz[j] = ok ? __ldg(tgt + 3 * j + 2) : 0.f;
+    }
+
+    static_assert(sizeof(PoseState) <= sizeof(S.state), "PoseState must fit SmemSym::state");
+    PoseState &st = *reinterpret_cast<PoseState *>(S.state);
+    double &b1t = S.bt[0], &b2t = S.bt[1];
+    if (t == 0) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            st.p[i] = A.params[(size_t)row * 8 + i];
+            st.m[i] = A.adam_m ? A.adam_m[(size_t)row * 8 + i] : 0.f;
+            st.v[i] = A.adam_v ? A.adam_v[(size_t)row * 8 + i] : 0.f;
+        }
+        b1t = pow((double)A.beta1, (double)A.step0);
+        b2t = pow((double)A.beta2, (double)A.step0);
+    }
+    const int abase = A.row_base ? A.row_base[row] : A.angle_base;
+    const float boff = (float)((double)abase * 3.14159274101257324 / 4.0);
+    const int k3d = A.k3d;
+
+    // role of this thread in the per-superblock column reduction: metric rm, column rc of the
+    // 128 columns (64 per half) finished in a round
+    const int rm = t >> 7, rh = (t >> 6) & 1, rc = t & 63;
+
+    for (int it = 0; it < A.iters; ++it) {
+        // ---- (a) pose from the 8 scalars
+        if (t == 0) pose_forward(st, boff, S.pose);
+        __syncthreads();
+        float Rm[9], Tv[3];
+#pragma unroll
+        for (int i = 0; i < 9; ++i) Rm[i] = S.pose[i];
+#pragma unroll
+        for (int i = 0; i < 3; ++i) Tv[i] = S.pose[9 + i];
+
+        // ---- (b) transform: y = R x + T  (bmm(src, R^T) + T, houv.py:102)
+        for (int i = t; i < pad; i += kSymThreads) {
+            if (i < N) {
+                const float x0 = __ldg(src + 3 * i), x1 = __ldg(src + 3 * i + 1),
+                            x2 = __ldg(src + 3 * i + 2);
+                S.yx[i] = __fadd_rn(__fmaf_rn(x2, Rm[2], __fmaf_rn(x1, Rm[1], __fmul_rn(x0, Rm[0]))), Tv[0]);
+                S.yy[i] = __fadd_rn(__fmaf_rn(x2, Rm[5], __fmaf_rn(x1, Rm[4], __fmul_rn(x0, Rm[3]))), Tv[1]);
+                S.yz[i] = __fadd_rn(__fmaf_rn(x2, Rm[8], __fmaf_rn(x1, Rm[7], __fmul_rn(x0, Rm[6]))), Tv[2]);
+            } else {
+                S.yx[i] = kInf; S.yy[i] = kInf; S.yz[i] = 0.f;
+            }
+        }
+        // row bookkeeping of this sweep: shadow = +inf, winning superblock = 0
+#pragma unroll
+        for (int k = 0; k < 32; ++k) S.shadow[k][t] = kInf;
+        for (int i = t; i < 4 * 2 * kPts / 4; i += kSymThreads)
+            reinterpret_cast<unsigned *>(&S.gid[0][0][0])[i] = 0u;
+        for (int i = t; i < 4 * kPts / 4; i += kSymThreads)
+            reinterpret_cast<unsigned *>(&S.rgid1[0][0])[i] = 0u;
+        __syncthreads();
+
+        // ---- (c) the symmetric sweep
+        float nqx[8], nqy[8], nqz[8], best[4][8];
+        if (scan_active) {
+#pragma unroll
+            for (int r = 0; r < 8; ++r) {
+                nqx[r] = -S.yx[row0 + r]; nqy[r] = -S.yy[row0 + r]; nqz[r] = -S.yz[row0 + r];
+            }
+        }
+#pragma unroll
+        for (int r = 0; r < 8; ++r)
+#pragma unroll
+            for (int m = 0; m < 4; ++m) best[m][r] = kInf;
+        float vcol = 0.f;  // sum sqrt(column minimum) of view metric rm (reducer role)
+
+#pragma unroll 1
+        for (int rr = 0; rr < nsbh; ++rr) {
+            const int sb = half * nsbh + rr;  // superblock swept by this half in this round
+            if (scan_active) {
+                const int sbbase = sb * kSB;
+#pragma unroll 1
+                for (int ph = 0; ph < 4; ++ph) {
+                    const int cb = (gq + ph) & 3;  // 16-column block of this group in this phase
+                    float2 cm[4];
+#pragma unroll
+                    for (int m = 0; m < 4; ++m) cm[m] = make_float2(kInf, kInf);
+                    const int cbase = sbbase + 16 * cb;
+#pragma unroll 2
+                    for (int s = 0; s < 8; ++s) {
+                        const int c = cbase + 2 * ((ll + s) & 7);
+                        const float2 X = *reinterpret_cast<const float2 *>(&S.tx[c]);
+                        const float2 Y = *reinterpret_cast<const float2 *>(&S.ty[c]);
+                        const float2 Z = *reinterpret_cast<const float2 *>(&S.tz[c]);
+                        sym_step(X, Y, Z, nqx, nqy, nqz, best, cm);
+                        if (s < 7) {  // the column pair moves on to lane ll-1; ours comes from ll+1
+#pragma unroll
+                            for (int m = 0; m < 4; ++m) {
+                                cm[m].x = __shfl_sync(0xffffffffu, cm[m].x, ll + 1, 8);
+                                cm[m].y = __shfl_sync(0xffffffffu, cm[m].y, ll + 1, 8);
+                            }
+                        }
+                    }
+                    // after step 7 this lane holds the finished pair (ll+7)&7 of block cb
+                    const int pc = 16 * cb + 2 * ((ll + 7) & 7);
+#pragma unroll
+                    for (int m = 0; m < 4; ++m)
+                        *reinterpret_cast<float2 *>(&S.part[half][sg][m][pc]) = cm[m];
+                }
+                // rows: did this superblock strictly improve the running minimum?
+#pragma unroll
+                for (int m = 0; m < 4; ++m)
+#pragma unroll
+                    for (int r = 0; r < 8; ++r) {
+                        const float prev = S.shadow[m * 8 + r][t];
+                        if (best[m][r] < prev) {
+                            S.shadow[m * 8 + r][t] = best[m][r];
+                            if (half) S.rgid1[m][row0 + r] = (unsigned char)sb;
+                            else S.gid[m][1][row0 + r] = (unsigned char)sb;
+                        }
+                    }
+            }
+            __syncthreads();
+            // columns: first sub-group (ascending rows) holding the minimum
+            {
+                const int col = (rh * nsbh + rr) * kSB + rc;
+                float bv = kInf;
+                int bs = 0;
+                for (int g = 0; g < nsg; ++g) {
+                    const float v = S.part[rh][g][rm][rc];
+                    if (v < bv) { bv = v; bs = g; }
+                }
+                S.gid[rm][0][col] = (unsigned char)bs;
+                if (rm == 0) S.d3[0][col] = bv;
+                else if (col < M) vcol += sqrtf(bv);
+            }
+            __syncthreads();
+        }
+
+        // ---- (d) rows: merge the two column halves (lower half wins ties = first minimum)
+        float vs[2][3] = {{0.f, 0.f, 0.f}, {0.f, 0.f, 0.f}};  // sum sqrt(d) of the view terms [dir][view]
+#pragma unroll
+        for (int m = 0; m < 3; ++m) vs[0][m] = (rm == m + 1) ? vcol : 0.f;
+        if (half == 0 && scan_active) {
+#pragma unroll
+            for (int m = 0; m < 4; ++m)
+#pragma unroll
+                for (int r = 0; r < 8; ++r) {
+                    const int i = row0 + r;
+                    float b = best[m][r];
+                    const float b1 = S.shadow[m * 8 + r][t + 256];
+                    if (b1 < b) {
+                        b = b1;
+                        S.gid[m][1][i] = S.rgid1[m][i];
+                    }
+                    if (i < N) {
+                        if (m == 0) S.d3[1][i] = b;
+                        else vs[1][m - 1] += sqrtf(b);
+                    }
+                }
+        }
+        __syncthreads();
+
+        // ---- (e) k-th smallest of d3[0][0..M) and d3[1][0..N): 4 x 8-bit radix select
+        unsigned prefix[2] = {0u, 0u};
+        int kk[2] = {k3d, k3d};
+#pragma unroll 1
+        for (int shift = 24; shift >= 0; shift -= 8) {
+            for (int b = t; b < 512; b += kSymThreads) (&S.hist[0][0])[b] = 0;
+            __syncthreads();
+#pragma unroll
+            for (int dir = 0; dir < 2; ++dir) {
+                const int len = dir ? N : M;
+                for (int q = t; q < len; q += kSymThreads) {
+                    const unsigned bits = __float_as_uint(S.d3[dir][q]);
+                    const bool match = (shift == 24) ||
+                                       ((bits >> (shift + 8)) == (prefix[dir] >> (shift + 8)));
+                    if (match) atomicAdd(&S.hist[dir][(bits >> shift) & 255u], 1);
+                }
+            }
+            __syncthreads();
+            if (t < 64) {
+                const int dir = t >> 5, ln = t & 31;
+                int c[8], s = 0;
+#pragma unroll
+                for (int b = 0; b < 8; ++b) { c[b] = S.hist[dir][8 * ln + b]; s += c[b]; }
+                int incl = s;
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) {
+                    int n = __shfl_up_sync(0xffffffffu, incl, o);
+                    if (ln >= o) incl += n;
+                }
+                const int excl = incl - s;
+                if (excl < kk[dir] && kk[dir] <= incl) {
+                    int rem = kk[dir] - excl, bin = 0, cnt = 0;
+                    bool done = false;
+#pragma unroll
+                    for (int b = 0; b < 8; ++b) {
+                        if (!done) {
+                            if (rem <= c[b]) { bin = 8 * ln + b; cnt = c[b]; done = true; }
+                            else rem -= c[b];
+                        }
+                    }
+                    S.selu[dir * 2] = prefix[dir] | ((unsigned)bin << shift);
+                    S.selu[dir * 2 + 1] = (unsigned)rem;
+                    S.selu[4 + dir] = (unsigned)cnt;  // after the last round: number of ties
+                }
+            }
+            __syncthreads();
+#pragma unroll
+            for (int dir = 0; dir < 2; ++dir) {
+                prefix[dir] = S.selu[dir * 2];
+                kk[dir] = (int)S.selu[dir * 2 + 1];
+            }
+        }
+        float thr[2], tiew[2];
+#pragma unroll
+        for (int dir = 0; dir < 2; ++dir) {
+            thr[dir] = __uint_as_float(prefix[dir]);
+            tiew[dir] = (float)kk[dir] / (float)S.selu[4 + dir];
+        }
+
+        // ---- (f) the eight directional means and the four min() selections
+        float sums[8];
+        sums[0] = 0.f; sums[1] = 0.f;
+#pragma unroll
+        for (int dir = 0; dir < 2; ++dir) {
+            const int len = dir ? N : M;
+            for (int q = t; q < len; q += kSymThreads) {
+                const float d = S.d3[dir][q];
+                if (d < thr[dir]) sums[dir] += sqrtf(d);
+            }
+#pragma unroll
+            for (int m = 0; m < 3; ++m) sums[2 + dir * 3 + m] = vs[dir][m];
+        }
+        block_sum_sym<8>(sums, S);
+        float cdv[4][2];  // [metric][dir]
+#pragma unroll
+        for (int dir = 0; dir < 2; ++dir) {
+            cdv[0][dir] = (sums[dir] + (float)kk[dir] * sqrtf(thr[dir])) / (float)k3d;
+#pragma unroll
+            for (int m = 0; m < 3; ++m) cdv[1 + m][dir] = sums[2 + dir * 3 + m] / (float)N;
+        }
+        int side[4];
+        float mins[4];
+#pragma unroll
+        for (int m = 0; m < 4; ++m) {  // torch.min over cat([dist1-side, dist2-side]): first wins ties
+            side[m] = cdv[m][1] < cdv[m][0] ? 1 : 0;
+            mins[m] = side[m] ? cdv[m][1] : cdv[m][0];
+        }
+        const float min_1 = mins[0];
+        const float loss = __fadd_rn(__fmul_rn(min_1, A.w3d),
+                                     __fmul_rn(A.wview, __fadd_rn(__fadd_rn(mins[1], mins[2]), mins[3])));
+        if (t == 0) {
+            if (A.trace) {
+                A.trace[((size_t)it * A.rows + row) * 2 + 0] = loss;
+                A.trace[((size_t)it * A.rows + row) * 2 + 1] = min_1;
+            }
+            if (it == A.iters - 1) {  // houv.py:134-138: results of the LAST forward
+                A.min1_out[row] = min_1;
+                if (A.loss_out) A.loss_out[row] = loss;
+#pragma unroll
+                for (int i = 0; i < 9; ++i) A.R_out[(size_t)row * 9 + i] = Rm[i];
+#pragma unroll
+                for (int i = 0; i < 3; ++i) A.T_out[(size_t)row * 3 + i] = Tv[i];
+            }
+        }
+
+        // ---- (h) gradient: only the side that won each min(); the exact arg-min is recovered
+        //          from the 64 candidates of the winning group.  Candidates are visited in a
+        //          lane-skewed order (different lanes hold different groups: same offset = same
+        //          bank), so the first minimum is taken lexicographically on (distance, index).
+        float acc[12];
+#pragma unroll
+        for (int i = 0; i < 12; ++i) acc[i] = 0.f;
+        const int lane = t & 31;
+#pragma unroll
+        for (int m = 0; m < 4; ++m) {
+            const int dir = side[m];
+            const float *qX = dir ? S.yx : S.tx, *qY = dir ? S.yy : S.ty, *qZ = dir ? S.yz : S.tz;
+            const float *tX = dir ? S.tx : S.yx, *tY = dir ? S.ty : S.yy, *tZ = dir ? S.tz : S.yz;
+            const int nq = dir ? N : M;
+            // d(mean over rows)/d(row) * weight / k      houv.py:124,222; m_u_c.py:94-95
+            const float coef = A.grad_scale * (m == 0 ? A.w3d : A.wview) / (float)(m == 0 ? k3d : N);
+            for (int q = t; q < nq; q += kSymThreads) {
+                float wt = 1.f;
+                if (m == 0) {  // top-k membership of the trimmed 3-D term
+                    const float d = S.d3[dir][q];
+                    wt = d < thr[dir] ? 1.f : (d == thr[dir] ? tiew[dir] : 0.f);
+                    if (wt == 0.f) continue;
+                }
+                const int j0 = (int)S.gid[m][dir][q] * kSB;
+                const float qx = qX[q], qy = qY[q], qz = qZ[q];
+                float bd = kInf;
+                int bj = j0;
+#pragma unroll 4
+                for (int k = 0; k < kSB / 2; ++k) {
+                    const int c = j0 + 2 * ((k + lane) & (kSB / 2 - 1));
+                    const float2 X = *reinterpret_cast<const float2 *>(&tX[c]);
+                    const float2 Y = *reinterpret_cast<const float2 *>(&tY[c]);
+                    const float2 Z = *reinterpret_cast<const float2 *>(&tZ[c]);
+                    const float d0 = metric_dist(m, X.x, Y.x, Z.x, qx, qy, qz);
+                    const float d1 = metric_dist(m, X.y, Y.y, Z.y, qx, qy, qz);
+                    if (d0 < bd || (d0 == bd && c < bj)) { bd = d0; bj = c; }
+                    if (d1 < bd || (d1 == bd && c + 1 < bj)) { bd = d1; bj = c + 1; }
+                }
+                // sqrt backward then chamfer backward (x2): d=0 gives inf*0 = NaN like autograd
+                const float gg = (coef * wt) / (2.f * sqrtf(bd)) * 2.f;
+                const float sgn = dir ? 1.f : -1.f;  // (transformed src point) - (tgt point)
+                float v0 = m == 1 ? 0.f : gg * (sgn * (qx - tX[bj]));
+                float v1 = m == 2 ? 0.f : gg * (sgn * (qy - tY[bj]));
+                float v2 = m == 3 ? 0.f : gg * (sgn * (qz - tZ[bj]));
+                const int xi = dir ? q : bj;  // which source point the gradient lands on
+                const float x0 = __ldg(src + 3 * xi), x1 = __ldg(src + 3 * xi + 1),
+                            x2 = __ldg(src + 3 * xi + 2);
+                acc[0] += v0 * x0; acc[1] += v0 * x1; acc[2] += v0 * x2;
+                acc[3] += v1 * x0; acc[4] += v1 * x1; acc[5] += v1 * x2;
+                acc[6] += v2 * x0; acc[7] += v2 * x1; acc[8] += v2 * x2;
+                acc[9] += v0; acc[10] += v1; acc[11] += v2;
+            }
+        }
+        block_sum_sym<12>(acc, S);
+
+        // ---- (i) closed-form pose backward + Adam on the 8 scalars
+        if (t == 0) {
+            float GR[3][3], gT[3], g[8];
+#pragma unroll
+            for (int i = 0; i < 3; ++i) {
+#pragma unroll
+                for (int j = 0; j < 3; ++j) GR[i][j] = acc[i * 3 + j];
+                gT[i] = acc[9 + i];
+            }
+            pose_backward(st, GR, gT, g);
+            adam_step(st, g, A, b1t, b2t);
+        }
+        __syncthreads();
+    }
+
+    if (t == 0) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            A.params[(size_t)row * 8 + i] = st.p[i];
+            if (A.adam_m) A.adam_m[(size_t)row * 8 + i] = st.m[i];
+            if (A.adam_v) A.adam_v[(size_t)row * 8 + i] = st.v[i];
+        }
+    }
+}
+
+int launch_pose_sym(const PoseArgs &a, cudaStream_t st) {
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(pose_sym_kernel,
+                                             cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             (int)sizeof(SmemSym));
+        if (e != cudaSuccess) return (int)e;
+        attr_set = true;
+    }
+    pose_sym_kernel<<<a.rows, kSymThreads, sizeof(SmemSym), st>>>(a);
+    return check_launch();
+}
+
+}  // namespace houv
