@@ -261,10 +261,13 @@ def run_ours(args):
     ms_e2e, _ = timed(step_e2e, args.steps)
     clocks = sampler.stop() if rank == 0 else None
 
-    # dominant kernel: executed FLOP = 2 directions x N*M x 13 FLOP per row-iteration
+    # dominant kernel (K3, symmetric scan).  Algorithmic work: 13 FLOP per directed
+    # four-metric point pair, 2*N*M directed pairs per row-iteration = 26*N*M.  The symmetric
+    # kernel evaluates d(i,j) once for both directions, so it EXECUTES 13*N*M; the reference's
+    # own arithmetic for the same result is 64*N*M (8 searches x 8 FLOP).
     kms = sum(a.elapsed_time(b) for a, b, *_ in ktim)
-    kflop = sum(26.0 * n * n * rows * iters for _, _, rows, iters, n in ktim)
-    kref = sum(64.0 * n * n * rows * iters for _, _, rows, iters, n in ktim)
+    kunits = sum(float(n) * n * rows * iters for _, _, rows, iters, n in ktim)
+    kflop, kexec, kref = 26.0 * kunits, 13.0 * kunits, 64.0 * kunits
     if rank != 0:
         return
     total_pairs = P * world * args.steps
@@ -289,12 +292,22 @@ def run_ours(args):
                 "h2d_bytes_per_step": int(h_src.numel() * 4 * 2 + h_gt.numel() * 4),
                 "d2h_bytes_per_step": int(h_out.numel() * 4)},
         "gpu_launches": launches,
-        "roofline": {"bound": "fp32", "kernel": "houv::pose_kernel (K3)",
+        "roofline": {"bound": "fp32", "kernel": "houv::pose_sym_kernel (K3, symmetric scan)",
                      "achieved": kflop / kms / 1e9, "peak": fp32_peak, "unit": "TFLOP/s",
                      "frac": kflop / kms / 1e9 / fp32_peak, "traffic": traffic,
                      "peak_source": "FFMA-chain probe run in this process (MEASURED_PEAKS.json "
                                     "holds no FP32 CUDA-core figure)",
+                     "basis": "algorithmic: 13 FLOP x 2*N*M directed four-metric point pairs per "
+                              "row-iteration (SURVEY 8d); the kernel shares one evaluation between "
+                              "the two directions, so executed_tflops is half of achieved",
+                     "executed_tflops": kexec / kms / 1e9,
+                     "executed_frac": kexec / kms / 1e9 / fp32_peak,
                      "ref_equiv_tflops": kref / kms / 1e9,
+                     # 9 FMA-pipe + 8 ALU-pipe (min) lane-cycles per evaluation; the two pipes
+                     # share register-file operand bandwidth and add up (tools/ubench/pipes.cu)
+                     "math_pipe_cycles_frac": (17.0 * kunits / (kms * 1e-3 * clocks["sm_mhz"] * 1e6
+                                                                * 148 * 128))
+                     if clocks and clocks.get("sm_mhz") else None,
                      "kernel_ms_per_launch": kms / max(len(ktim), 1),
                      "kernel_share_of_step": kms / ms_dev,
                      "flop_per_launch": kflop / max(len(ktim), 1)},

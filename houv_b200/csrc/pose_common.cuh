@@ -40,6 +40,22 @@ __device__ __forceinline__ float metric_dist(int m, float tx, float ty, float tz
     return __fmaf_rn(dx, dx, yy);
 }
 
+// the same for two targets at once (packed FADD2/FMUL2/FFMA2)
+__device__ __forceinline__ float2 metric_dist2(int m, float2 tx, float2 ty, float2 tz, float qx,
+                                               float qy, float qz) {
+    const float2 dz = __fadd2_rn(tz, make_float2(-qz, -qz));
+    if (m == 2) {
+        const float2 dx = __fadd2_rn(tx, make_float2(-qx, -qx));
+        return __ffma2_rn(dz, dz, __fmul2_rn(dx, dx));
+    }
+    const float2 dy = __fadd2_rn(ty, make_float2(-qy, -qy));
+    const float2 yy = __fmul2_rn(dy, dy);
+    if (m == 1) return __ffma2_rn(dz, dz, yy);
+    const float2 dx = __fadd2_rn(tx, make_float2(-qx, -qx));
+    const float2 xy = __ffma2_rn(dx, dx, yy);
+    return m == 0 ? __ffma2_rn(dz, dz, xy) : xy;
+}
+
 // Per-row optimiser state, live in thread 0's registers for the whole kernel.
 struct PoseState {
     float p[8], m[8], v[8];
@@ -139,6 +155,6 @@ __device__ __forceinline__ void adam_step(PoseState &s, const float (&g)[8], con
     }
 }
 
-int launch_pose_sym(const PoseArgs &a, cudaStream_t st);  // pose_sym.cu
+int launch_pose_sym(const PoseArgs &a, int unroll, cudaStream_t st);  // pose_sym.cu
 
 }  // namespace houv

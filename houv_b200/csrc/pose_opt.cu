@@ -422,7 +422,7 @@ __global__ void __launch_bounds__(kThreads, 2) pose_kernel(const PoseArgs A) {
 }
 
 static int g_pose_variant = -1;
-constexpr int kDefaultPoseVariant = 0;  // 0..5: two directed scans (this file); 10: symmetric scan (pose_sym.cu)
+constexpr int kDefaultPoseVariant = 12;  // 0..5: two directed scans (this file); 10: symmetric scan (pose_sym.cu)
 
 template <int kQ, int H, int U>
 static int launch_pose(const PoseArgs &a, cudaStream_t st) {
@@ -481,7 +481,9 @@ extern "C" int houv_pose_optimise(const float *src, const float *tgt, int P, int
         g_pose_variant = e ? atoi(e) : kDefaultPoseVariant;
     }
     switch (g_pose_variant) {
-        case 10: return launch_pose_sym(a, st);
+        case 10: return launch_pose_sym(a, 2, st);
+        case 11: return launch_pose_sym(a, 4, st);
+        case 12: return launch_pose_sym(a, 8, st);
         case 1: return launch_pose<4, 1, 2>(a, st);
         case 2: return launch_pose<4, 2, 1>(a, st);
         case 3: return launch_pose<2, 1, 2>(a, st);

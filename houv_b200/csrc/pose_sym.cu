@@ -40,6 +40,7 @@ constexpr int kSB = 64;        // columns per superblock = rows per sub-group = 
 constexpr int kRowsPerThread = 8;
 
 struct SmemSym {
+    // NB the gradient phase addresses y and z as x + kPts and x + 2*kPts: keep the order
     float tx[kPts], ty[kPts], tz[kPts];   // target cloud (columns), fixed
     float yx[kPts], yy[kPts], yz[kPts];   // transformed source (rows) of this iteration
     float d3[2][kPts];                    // 3-D metric: [0] = column minima (dist1), [1] = row minima (dist2)
@@ -98,7 +99,7 @@ __device__ __forceinline__ void eval4(const float2 X, const float2 Y, const floa
 __device__ __forceinline__ void sym_step(const float2 X, const float2 Y, const float2 Z,
                                          const float (&nqx)[8], const float (&nqy)[8],
                                          const float (&nqz)[8], float (&best)[4][8],
-                                         float2 (&cm)[4]) {
+                                         float (&cmx)[4], float (&cmy)[4]) {
 #pragma unroll
     for (int r = 0; r < 8; r += 2) {
         float2 v0[4], v1[4];
@@ -108,12 +109,14 @@ __device__ __forceinline__ void sym_step(const float2 X, const float2 Y, const f
         for (int m = 0; m < 4; ++m) {
             best[m][r] = min3(best[m][r], v0[m].x, v0[m].y);
             best[m][r + 1] = min3(best[m][r + 1], v1[m].x, v1[m].y);
-            cm[m].x = min3(cm[m].x, v0[m].x, v1[m].x);
-            cm[m].y = min3(cm[m].y, v0[m].y, v1[m].y);
+            cmx[m] = min3(cmx[m], v0[m].x, v1[m].x);
+            cmy[m] = min3(cmy[m], v0[m].y, v1[m].y);
         }
     }
 }
 
+// kSymUnroll: unroll of the 8 rotation steps of a phase
+template <int kSymUnroll>
 __global__ void __launch_bounds__(kSymThreads, 1) pose_sym_kernel(const PoseArgs A) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     SmemSym &S = *reinterpret_cast<SmemSym *>(smem_raw);
@@ -221,22 +224,22 @@ __global__ void __launch_bounds__(kSymThreads, 1) pose_sym_kernel(const PoseArgs
 #pragma unroll 1
                 for (int ph = 0; ph < 4; ++ph) {
                     const int cb = (gq + ph) & 3;  // 16-column block of this group in this phase
-                    float2 cm[4];
+                    float cmx[4], cmy[4];  // running column minima of the pair in hand
 #pragma unroll
-                    for (int m = 0; m < 4; ++m) cm[m] = make_float2(kInf, kInf);
+                    for (int m = 0; m < 4; ++m) { cmx[m] = kInf; cmy[m] = kInf; }
                     const int cbase = sbbase + 16 * cb;
-#pragma unroll 2
+#pragma unroll kSymUnroll
                     for (int s = 0; s < 8; ++s) {
                         const int c = cbase + 2 * ((ll + s) & 7);
                         const float2 X = *reinterpret_cast<const float2 *>(&S.tx[c]);
                         const float2 Y = *reinterpret_cast<const float2 *>(&S.ty[c]);
                         const float2 Z = *reinterpret_cast<const float2 *>(&S.tz[c]);
-                        sym_step(X, Y, Z, nqx, nqy, nqz, best, cm);
+                        sym_step(X, Y, Z, nqx, nqy, nqz, best, cmx, cmy);
                         if (s < 7) {  // the column pair moves on to lane ll-1; ours comes from ll+1
 #pragma unroll
                             for (int m = 0; m < 4; ++m) {
-                                cm[m].x = __shfl_sync(0xffffffffu, cm[m].x, ll + 1, 8);
-                                cm[m].y = __shfl_sync(0xffffffffu, cm[m].y, ll + 1, 8);
+                                cmx[m] = __shfl_sync(0xffffffffu, cmx[m], ll + 1, 8);
+                                cmy[m] = __shfl_sync(0xffffffffu, cmy[m], ll + 1, 8);
                             }
                         }
                     }
@@ -244,7 +247,7 @@ __global__ void __launch_bounds__(kSymThreads, 1) pose_sym_kernel(const PoseArgs
                     const int pc = 16 * cb + 2 * ((ll + 7) & 7);
 #pragma unroll
                     for (int m = 0; m < 4; ++m)
-                        *reinterpret_cast<float2 *>(&S.part[half][sg][m][pc]) = cm[m];
+                        *reinterpret_cast<float2 *>(&S.part[half][sg][m][pc]) = make_float2(cmx[m], cmy[m]);
                 }
                 // rows: did this superblock strictly improve the running minimum?
 #pragma unroll
@@ -416,8 +419,8 @@ __global__ void __launch_bounds__(kSymThreads, 1) pose_sym_kernel(const PoseArgs
 #pragma unroll
         for (int m = 0; m < 4; ++m) {
             const int dir = side[m];
-            const float *qX = dir ? S.yx : S.tx, *qY = dir ? S.yy : S.ty, *qZ = dir ? S.yz : S.tz;
-            const float *tX = dir ? S.tx : S.yx, *tY = dir ? S.ty : S.yy, *tZ = dir ? S.tz : S.yz;
+            // x, y, z of a cloud are consecutive kPts-float arrays: one base pointer per cloud
+            const float *qB = dir ? S.yx : S.tx, *tB = dir ? S.tx : S.yx;
             const int nq = dir ? N : M;
             // d(mean over rows)/d(row) * weight / k      houv.py:124,222; m_u_c.py:94-95
             const float coef = A.grad_scale * (m == 0 ? A.w3d : A.wview) / (float)(m == 0 ? k3d : N);
@@ -429,26 +432,26 @@ __global__ void __launch_bounds__(kSymThreads, 1) pose_sym_kernel(const PoseArgs
                     if (wt == 0.f) continue;
                 }
                 const int j0 = (int)S.gid[m][dir][q] * kSB;
-                const float qx = qX[q], qy = qY[q], qz = qZ[q];
+                const float qx = qB[q], qy = qB[kPts + q], qz = qB[2 * kPts + q];
                 float bd = kInf;
                 int bj = j0;
 #pragma unroll 4
                 for (int k = 0; k < kSB / 2; ++k) {
                     const int c = j0 + 2 * ((k + lane) & (kSB / 2 - 1));
-                    const float2 X = *reinterpret_cast<const float2 *>(&tX[c]);
-                    const float2 Y = *reinterpret_cast<const float2 *>(&tY[c]);
-                    const float2 Z = *reinterpret_cast<const float2 *>(&tZ[c]);
-                    const float d0 = metric_dist(m, X.x, Y.x, Z.x, qx, qy, qz);
-                    const float d1 = metric_dist(m, X.y, Y.y, Z.y, qx, qy, qz);
-                    if (d0 < bd || (d0 == bd && c < bj)) { bd = d0; bj = c; }
-                    if (d1 < bd || (d1 == bd && c + 1 < bj)) { bd = d1; bj = c + 1; }
+                    const float2 X = *reinterpret_cast<const float2 *>(&tB[c]);
+                    const float2 Y = *reinterpret_cast<const float2 *>(&tB[kPts + c]);
+                    const float2 Z = *reinterpret_cast<const float2 *>(&tB[2 * kPts + c]);
+                    const float2 d = metric_dist2(m, X, Y, Z, qx, qy, qz);
+                    // first minimum = lexicographic minimum of (distance, index)
+                    if (d.x < bd || (d.x == bd && c < bj)) { bd = d.x; bj = c; }
+                    if (d.y < bd || (d.y == bd && c + 1 < bj)) { bd = d.y; bj = c + 1; }
                 }
                 // sqrt backward then chamfer backward (x2): d=0 gives inf*0 = NaN like autograd
                 const float gg = (coef * wt) / (2.f * sqrtf(bd)) * 2.f;
                 const float sgn = dir ? 1.f : -1.f;  // (transformed src point) - (tgt point)
-                float v0 = m == 1 ? 0.f : gg * (sgn * (qx - tX[bj]));
-                float v1 = m == 2 ? 0.f : gg * (sgn * (qy - tY[bj]));
-                float v2 = m == 3 ? 0.f : gg * (sgn * (qz - tZ[bj]));
+                float v0 = m == 1 ? 0.f : gg * (sgn * (qx - tB[bj]));
+                float v1 = m == 2 ? 0.f : gg * (sgn * (qy - tB[kPts + bj]));
+                float v2 = m == 3 ? 0.f : gg * (sgn * (qz - tB[2 * kPts + bj]));
                 const int xi = dir ? q : bj;  // which source point the gradient lands on
                 const float x0 = __ldg(src + 3 * xi), x1 = __ldg(src + 3 * xi + 1),
                             x2 = __ldg(src + 3 * xi + 2);
@@ -485,17 +488,26 @@ __global__ void __launch_bounds__(kSymThreads, 1) pose_sym_kernel(const PoseArgs
     }
 }
 
-int launch_pose_sym(const PoseArgs &a, cudaStream_t st) {
+template <int kU>
+static int launch_sym(const PoseArgs &a, cudaStream_t st) {
     static bool attr_set = false;
     if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(pose_sym_kernel,
+        cudaError_t e = cudaFuncSetAttribute(pose_sym_kernel<kU>,
                                              cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              (int)sizeof(SmemSym));
         if (e != cudaSuccess) return (int)e;
         attr_set = true;
     }
-    pose_sym_kernel<<<a.rows, kSymThreads, sizeof(SmemSym), st>>>(a);
+    pose_sym_kernel<kU><<<a.rows, kSymThreads, sizeof(SmemSym), st>>>(a);
     return check_launch();
+}
+
+int launch_pose_sym(const PoseArgs &a, int unroll, cudaStream_t st) {
+    switch (unroll) {
+        case 4: return launch_sym<4>(a, st);
+        case 8: return launch_sym<8>(a, st);
+        default: return launch_sym<2>(a, st);
+    }
 }
 
 }  // namespace houv
