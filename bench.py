@@ -167,6 +167,40 @@ def workload_config(args):
 
 
 # ----------------------------------------------------------------- GPU arm
+def chamfer_nn_lines(dev, flush, fp32_peak):
+    """chamfer_3DDist forward at BASELINE configs C2 / C5 and at the HOUV batch shape
+    (6400 rows = 100 pairs x 64 starts): Gpts^2/s = 2*B*N*M / t / 1e9, 8 FLOP per directed
+    point pair against the FP32 peak.  CUDA events, L2 flushed between iterations."""
+    import torch
+    from houv_b200.chamfer import chamfer_3D
+    out = {}
+    for name, (B, N, M) in (("C2_b32_2048x2048", (32, 2048, 2048)),
+                            ("C5_b64_16384x2048", (64, 16384, 2048)),
+                            ("houv_batch_b6400_2048x2048", (6400, 2048, 2048))):
+        torch.manual_seed(0)
+        x1 = torch.rand(B, N, 3, device=dev)
+        x2 = torch.rand(B, M, 3, device=dev)
+        d1 = torch.empty(B, N, device=dev); d2 = torch.empty(B, M, device=dev)
+        i1 = torch.empty(B, N, device=dev, dtype=torch.int32)
+        i2 = torch.empty(B, M, device=dev, dtype=torch.int32)
+        ts = []
+        for i in range(8):
+            flush.add_(1.0)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            chamfer_3D.forward(x1, x2, d1, d2, i1, i2)
+            e1.record()
+            torch.cuda.synchronize()
+            if i >= 3:
+                ts.append(e0.elapsed_time(e1))
+        ms = statistics.median(ts)
+        pairs = 2.0 * B * N * M
+        out[name] = {"ms": ms, "Gpts2_per_s": pairs / ms / 1e6,
+                     "frac_fp32_peak": 8.0 * pairs / ms / 1e9 / fp32_peak}
+        del x1, x2, d1, d2, i1, i2
+    return out
+
+
 def run_ours(args):
     import ctypes
     import numpy as np
@@ -317,6 +351,9 @@ def run_ours(args):
                     "trans_err_mean": float(met[:, 1].mean()),
                     "mse_mean": float(met[:, 2].mean())},
     }
+    # second half of BASELINE.json's metric: Chamfer NN throughput of the operator on its own
+    # (K1; chamfer_3DDist forward, both directions), directed point pairs per second
+    line["chamfer_nn"] = chamfer_nn_lines(dev, flush, fp32_peak)
     if world == 1 and not args.no_cpu_baseline:
         cores = os.cpu_count() or 1
         torch.set_num_threads(cores)

@@ -15,6 +15,8 @@ _cf = ctypes.c_float
 # name -> argtypes; every entry point returns int (0 = ok) unless noted
 _SIGNATURES = {
     "houv_chamfer3d_forward": [_vp, _vp, _ci, _ci, _ci, _vp, _vp, _vp, _vp, _vp],
+    "houv_chamfer3d_forward_ws": [_vp, _vp, _ci, _ci, _ci, _vp, _vp, _vp, _vp, _vp,
+                                  ctypes.c_size_t, _vp],
     "houv_nn_search": [_vp, _vp, _ci, _ci, _ci, _vp, _vp, _vp],
     "houv_chamfer3d_backward": [_vp, _vp, _vp, _vp, _vp, _vp, _ci, _ci, _ci, _vp, _vp, _vp],
     "houv_kabsch": [_vp, _vp, _vp, _ci, _ci, _vp, _vp, _vp],
@@ -28,7 +30,7 @@ _SIGNATURES = {
     "houv_fp32_probe": [_vp, _ci, _ci, ctypes.POINTER(ctypes.c_double), _vp],
 }
 
-EXPORTS = tuple(_SIGNATURES) + ("houv_version",)
+EXPORTS = tuple(_SIGNATURES) + ("houv_version", "houv_chamfer3d_workspace_bytes")
 
 
 def lib_path():
@@ -45,6 +47,8 @@ def load():
             fn = getattr(lib, name)
             fn.argtypes = args
             fn.restype = _ci
+        lib.houv_chamfer3d_workspace_bytes.restype = ctypes.c_size_t
+        lib.houv_chamfer3d_workspace_bytes.argtypes = [_ci, _ci, _ci]
         lib.houv_version.restype = ctypes.c_char_p
         lib.houv_version.argtypes = []
         _LIB = lib

@@ -26,11 +26,17 @@ class _Chamfer3DModule:
     def forward(xyz1, xyz2, dist1, dist2, idx1, idx2):
         B, N, _ = xyz1.shape
         M = xyz2.shape[1]
+        lib = _lib.load()
+        # scratch for the symmetric kernel when the larger cloud spans several 2048-row CTAs
+        # (caller-owned like every other buffer: the C ABI never allocates)
+        need = lib.houv_chamfer3d_workspace_bytes(B, N, M)
+        ws = torch.empty(need, dtype=torch.uint8, device=xyz1.device) if need else None
         with torch.cuda.device(xyz1.device):
-            rc = _lib.load().houv_chamfer3d_forward(
+            rc = lib.houv_chamfer3d_forward_ws(
                 xyz1.data_ptr(), xyz2.data_ptr(), B, N, M, dist1.data_ptr(), dist2.data_ptr(),
-                idx1.data_ptr(), idx2.data_ptr(), _lib.stream_ptr())
-        _lib.check(rc, "houv_chamfer3d_forward")
+                idx1.data_ptr(), idx2.data_ptr(), ws.data_ptr() if need else 0, need,
+                _lib.stream_ptr())
+        _lib.check(rc, "houv_chamfer3d_forward_ws")
         _lib.count_launches(1)
         return 1
 

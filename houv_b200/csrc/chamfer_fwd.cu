@@ -212,9 +212,24 @@ extern "C" int houv_nn_search(const float *query, const float *target, int B, in
     return dispatch_nn(a, 1, st);
 }
 
-extern "C" int houv_chamfer3d_forward(const float *xyz1, const float *xyz2, int B, int N, int M,
-                                      float *dist1, float *dist2, int *idx1, int *idx2,
-                                      void *stream) {
+// Symmetric kernel or two directed scans?  The symmetric kernel needs whole 2048-row CTAs to
+// fill the GPU (it does ~half the arithmetic but comes in coarse units).
+static bool want_symmetric(int B, int nr, long long ctas) {
+    if (g_nn_variant == 10) return true;
+    if (g_nn_variant >= 0) return false;
+    return nr >= 1024 && ctas >= 148;
+}
+
+extern "C" size_t houv_chamfer3d_workspace_bytes(int B, int N, int M) {
+    if (B <= 0 || N <= 0 || M <= 0) return 0;
+    const int nr = N >= M ? N : M, nc = N >= M ? M : N;
+    if (nr <= kSymChunkRows) return 0;
+    return sizeof(unsigned long long) * (size_t)B * (size_t)nc;
+}
+
+extern "C" int houv_chamfer3d_forward_ws(const float *xyz1, const float *xyz2, int B, int N, int M,
+                                         float *dist1, float *dist2, int *idx1, int *idx2,
+                                         void *workspace, size_t workspace_bytes, void *stream) {
     if (int e = check_sizes(B, N, M)) return e;
     if (B == 0 || (N == 0 && M == 0)) return 0;
     if (N == 0 || M == 0) {  // one side empty: each direction degenerates separately
@@ -222,9 +237,32 @@ extern "C" int houv_chamfer3d_forward(const float *xyz1, const float *xyz2, int 
         return houv_nn_search(xyz2, xyz1, B, M, N, dist2, idx2, stream);
     }
     if (!xyz1 || !xyz2 || !dist1 || !dist2 || !idx1 || !idx2) return HOUV_E_BADARG;
+    // rows = the larger cloud (chunked over CTAs), columns = the smaller one (streamed)
+    const bool one_rows = N >= M;
+    const int nr = one_rows ? N : M, nc = one_rows ? M : N;
+    const long long chunks = (nr + kSymChunkRows - 1) / kSymChunkRows;
+    const size_t need = houv_chamfer3d_workspace_bytes(B, N, M);
+    const bool ws_ok = need == 0 || (workspace && workspace_bytes >= need &&
+                                     (reinterpret_cast<uintptr_t>(workspace) & 7) == 0);
+    if (ws_ok && want_symmetric(B, nr, chunks * B)) {
+        SymArgs s;
+        s.rows = one_rows ? xyz1 : xyz2; s.cols = one_rows ? xyz2 : xyz1;
+        s.dist_r = one_rows ? dist1 : dist2; s.idx_r = one_rows ? idx1 : idx2;
+        s.dist_c = one_rows ? dist2 : dist1; s.idx_c = one_rows ? idx2 : idx1;
+        s.keys = need ? static_cast<unsigned long long *>(workspace) : nullptr;
+        s.B = B; s.nr = nr; s.nc = nc;
+        return launch_chamfer_sym(s, (cudaStream_t)stream);
+    }
     NNArgs a;
     a.B = B;
     a.dir[0] = NNDir{xyz1, xyz2, dist1, idx1, N, M};
     a.dir[1] = NNDir{xyz2, xyz1, dist2, idx2, M, N};
     return dispatch_nn(a, 2, (cudaStream_t)stream);
+}
+
+extern "C" int houv_chamfer3d_forward(const float *xyz1, const float *xyz2, int B, int N, int M,
+                                      float *dist1, float *dist2, int *idx1, int *idx2,
+                                      void *stream) {
+    return houv_chamfer3d_forward_ws(xyz1, xyz2, B, N, M, dist1, dist2, idx1, idx2, nullptr, 0,
+                                     stream);
 }

@@ -1,0 +1,337 @@
+// K1s -- symmetric brute-force Chamfer forward for sm_100a: every distance d(i,j) between
+// xyz1_i and xyz2_j is evaluated ONCE and folded into both results of
+// chamfer_cuda_forward (/root/reference/utils/metrics/CD/chamfer3D/chamfer3D.cu:136-154):
+// the row minimum (dist1/idx1 of NmDistanceKernel(xyz1 -> xyz2), :142) and the column minimum
+// (dist2/idx2 of NmDistanceKernel(xyz2 -> xyz1), :143).  The two launches of the reference
+// compute the same matrix: (b-a) and (a-b) square to the same float, and the contraction
+// fma(dz,dz,fma(dx,dx,dy*dy)) (chamfer3D.cu:32-35 as nvcc compiles it) is sign-symmetric,
+// so sharing the evaluation changes no bit of dist or idx.
+//
+// Schedule (same rotation as the K3 symmetric sweep, csrc/pose_sym.cu):
+//  * one CTA of 256 threads owns a chunk of 2048 rows of one batch element, 8 rows per thread
+//    in registers, and sweeps ALL columns; grid = (row chunks, batch);
+//  * columns are staged per 2048-column tile: the AoS tile comes in with ONE TMA bulk copy
+//    (cp.async.bulk + mbarrier) into a landing buffer and is transposed to SoA x[] y[] z[];
+//  * in every step a lane evaluates its 8 rows against one PAIR of columns with packed fp32
+//    (FADD2/FMUL2/FFMA2: 6 lane-ops per evaluation); the pair's running column minima travel
+//    with it from lane to lane inside 8-lane groups (2 SHFL per 16 evaluations);
+//  * minima only are tracked (one FMNMX3 per row per step, one per row pair and column);
+//    arg-mins are recovered afterwards from 64 candidates: rows remember the superblock (64
+//    columns) that last strictly improved them, columns get the first 64-row sub-group holding
+//    their minimum from a per-superblock reduction; the candidate equal to the known minimum
+//    with the smallest index is the reference's first minimum (chamfer3D.cu:36,46,126);
+//  * with more than one row chunk the column results of the chunks are combined with a 64-bit
+//    atomicMin on (distance bits << 32 | index) keys in a caller-provided workspace.
+// Cost per evaluation: 6 FMA-pipe + 2 ALU-pipe lane-cycles for BOTH directions, against
+// 2 x (6 + 1) in the two-scan kernel (chamfer_fwd.cu).
+#include "common.cuh"
+
+namespace houv {
+
+constexpr int kSRows = kSymChunkRows;  // rows per CTA (2048)
+constexpr int kSThreads = 256;
+constexpr int kSTile = 2048;     // columns resident per tile
+constexpr int kSGrp = 64;        // superblock / sub-group width
+constexpr int kPartStride = 66;  // floats per sub-group row of the partial-minimum buffer
+
+struct SmemK1s {
+    float cx[kSTile], cy[kSTile], cz[kSTile];  // column tile, SoA (y = x + kSTile, z = x + 2 kSTile)
+    float rx[kSRows], ry[kSRows], rz[kSRows];  // this CTA's rows, SoA
+    float stage[kSTile * 3];                   // TMA landing buffer (AoS tile)
+    float part[2][32][kPartStride];            // [buffer][sub-group][column of the superblock]
+    float cmin[kSTile];                        // column minima of the tile
+    unsigned char csg[kSTile];                 // first sub-group holding the column minimum
+    unsigned long long mbar;
+};
+
+__device__ __forceinline__ unsigned smem_u32(const void *p) {
+    return (unsigned)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ void mbar_init(unsigned long long *bar, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long *bar, unsigned bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)),
+                 "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void *dst, const void *src, unsigned bytes,
+                                         unsigned long long *bar) {
+    asm volatile(
+        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::
+            "r"(smem_u32(dst)),
+        "l"(src), "r"(bytes), "r"(smem_u32(bar))
+        : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long *bar, unsigned parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONE_%=;\n"
+        "bra WAIT_%=;\n"
+        "DONE_%=:\n"
+        "}\n" ::"r"(smem_u32(bar)),
+        "r"(parity)
+        : "memory");
+}
+
+// squared distances of one row against a column pair; nq* = negated row coordinates
+__device__ __forceinline__ float2 sqdist2b(float2 X, float2 Y, float2 Z, float nqx, float nqy,
+                                           float nqz) {
+    const float2 dx = __fadd2_rn(X, make_float2(nqx, nqx));
+    const float2 dy = __fadd2_rn(Y, make_float2(nqy, nqy));
+    const float2 dz = __fadd2_rn(Z, make_float2(nqz, nqz));
+    return __ffma2_rn(dz, dz, __ffma2_rn(dx, dx, __fmul2_rn(dy, dy)));
+}
+
+// smallest index j0+c (c < 64) whose distance to (qx,qy,qz) equals `target`, candidates read
+// from SoA arrays base[], base[stride + ...], base[2 stride + ...] in a lane-skewed order
+__device__ __forceinline__ int first_equal(const float *base, int stride, int j0, float qx,
+                                           float qy, float qz, float target, int lane) {
+    int bi = 0x7fffffff;
+#pragma unroll 4
+    for (int k = 0; k < kSGrp / 2; ++k) {
+        const int c = j0 + 2 * ((k + lane) & (kSGrp / 2 - 1));
+        const float2 X = *reinterpret_cast<const float2 *>(base + c);
+        const float2 Y = *reinterpret_cast<const float2 *>(base + stride + c);
+        const float2 Z = *reinterpret_cast<const float2 *>(base + 2 * stride + c);
+        const float2 d = sqdist2b(X, Y, Z, -qx, -qy, -qz);
+        if (d.y == target) bi = min(bi, c + 1);
+        if (d.x == target) bi = min(bi, c);
+    }
+    return bi == 0x7fffffff ? j0 : bi;
+}
+
+template <int kU>
+__global__ void __launch_bounds__(kSThreads, 2) chamfer_sym_kernel(const SymArgs A) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    SmemK1s &S = *reinterpret_cast<SmemK1s *>(smem_raw);
+    const int t = threadIdx.x;
+    const int w = t >> 5, l = t & 31;
+    const int gq = l >> 3, ll = l & 7;  // 8-lane rotation group, lane within it
+    const int sg = w * 4 + gq;          // 64-row sub-group: rows 64*sg .. 64*sg+63 of the chunk
+    const int row0 = 8 * t;
+    const int rbase = blockIdx.x * kSRows;
+    const int nr = A.nr, nc = A.nc;
+    const int nrows = min(kSRows, nr - rbase);  // real rows of this chunk (> 0 by grid size)
+    const bool scan_active = 256 * w < nrows;   // warp-uniform
+    const int nsg = (nrows + kSGrp - 1) / kSGrp;
+    const float inf = __int_as_float(0x7f800000);
+
+    if (t == 0) {
+        mbar_init(&S.mbar, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    unsigned phase = 0;
+    __syncthreads();
+
+    for (int b = blockIdx.y; b < A.B; b += gridDim.y) {
+        __syncthreads();  // the previous batch element's column recovery still reads rx/ry/rz
+        const float *rp = A.rows + ((size_t)b * nr + rbase) * 3;
+        const float *cp = A.cols + (size_t)b * nc * 3;
+
+        // ---- this thread's 8 rows: registers (negated) + shared SoA copy for the column side
+        float nqx[8], nqy[8], nqz[8], best[8], prev[8];
+        int gid[8], idxr[8];
+#pragma unroll
+        for (int r = 0; r < 8; ++r) {
+            const int i = row0 + r;
+            const bool ok = i < nrows;
+            const float x = ok ? __ldg(rp + 3 * i + 0) : inf;  // padded row: every distance inf/NaN
+            const float y = ok ? __ldg(rp + 3 * i + 1) : inf;
+            const float z = ok ? __ldg(rp + 3 * i + 2) : 0.f;
+            S.rx[i] = x; S.ry[i] = y; S.rz[i] = z;
+            nqx[r] = -x; nqy[r] = -y; nqz[r] = -z;
+            best[r] = inf; prev[r] = inf; gid[r] = 0; idxr[r] = 0;
+        }
+
+        for (int t0 = 0; t0 < nc; t0 += kSTile) {
+            const int cnt = min(kSTile, nc - t0);
+            const int cnt_pad = (cnt + kSGrp - 1) / kSGrp * kSGrp;
+            const int nsb = cnt_pad / kSGrp;
+            const int sb0 = t0 / kSGrp;  // global number of this tile's first superblock
+            const float *src = cp + (size_t)t0 * 3;
+            __syncthreads();  // previous tile / batch element fully consumed (cx.., stage, cmin, rx..)
+
+            // ---- stage the tile: one TMA bulk copy of the 16-byte-aligned part, AoS -> SoA
+            const bool al16 = (reinterpret_cast<uintptr_t>(src) & 15) == 0;
+            const int nb = al16 ? (cnt & ~3) : 0;  // points brought in by the bulk copy
+            if (nb > 0) {
+                if (t == 0) {
+                    // order the generic-proxy reads of `stage` (previous tile) before the async write
+                    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                    mbar_expect_tx(&S.mbar, (unsigned)nb * 12u);
+                    bulk_g2s(S.stage, src, (unsigned)nb * 12u, &S.mbar);
+                }
+                mbar_wait(&S.mbar, phase);
+                phase ^= 1u;
+                for (int p = t; p < nb / 4; p += kSThreads) {
+                    const float4 *s4 = reinterpret_cast<const float4 *>(S.stage) + 3 * p;
+                    const float4 a = s4[0], bb = s4[1], c = s4[2];
+                    reinterpret_cast<float4 *>(S.cx)[p] = make_float4(a.x, a.w, bb.z, c.y);
+                    reinterpret_cast<float4 *>(S.cy)[p] = make_float4(a.y, bb.x, bb.w, c.z);
+                    reinterpret_cast<float4 *>(S.cz)[p] = make_float4(a.z, bb.y, c.x, c.w);
+                }
+            }
+            for (int p = nb + t; p < cnt_pad; p += kSThreads) {  // unaligned tail and +inf padding
+                const bool ok = p < cnt;
+                S.cx[p] = ok ? __ldg(src + 3 * p + 0) : inf;
+                S.cy[p] = ok ? __ldg(src + 3 * p + 1) : 0.f;
+                S.cz[p] = ok ? __ldg(src + 3 * p + 2) : 0.f;
+            }
+            __syncthreads();
+
+            // ---- symmetric sweep of the tile, one superblock (64 columns) per round
+            unsigned dirty = 0;  // rows improved in this tile
+            int buf = 0;
+#pragma unroll 1
+            for (int sb = 0; sb < nsb; ++sb) {
+                if (scan_active) {
+#pragma unroll 1
+                    for (int ph = 0; ph < 4; ++ph) {
+                        const int cb = (gq + ph) & 3;
+                        const int cbase = sb * kSGrp + 16 * cb;
+                        float cmx = inf, cmy = inf;  // running minima of the column pair in hand
+#pragma unroll kU
+                        for (int s = 0; s < 8; ++s) {
+                            const int c = cbase + 2 * ((ll + s) & 7);
+                            const float2 X = *reinterpret_cast<const float2 *>(&S.cx[c]);
+                            const float2 Y = *reinterpret_cast<const float2 *>(&S.cy[c]);
+                            const float2 Z = *reinterpret_cast<const float2 *>(&S.cz[c]);
+#pragma unroll
+                            for (int r = 0; r < 8; r += 2) {
+                                const float2 d0 = sqdist2b(X, Y, Z, nqx[r], nqy[r], nqz[r]);
+                                const float2 d1 = sqdist2b(X, Y, Z, nqx[r + 1], nqy[r + 1], nqz[r + 1]);
+                                best[r] = min3(best[r], d0.x, d0.y);
+                                best[r + 1] = min3(best[r + 1], d1.x, d1.y);
+                                cmx = min3(cmx, d0.x, d1.x);
+                                cmy = min3(cmy, d0.y, d1.y);
+                            }
+                            if (s < 7) {  // the pair moves on to lane ll-1, ours arrives from ll+1
+                                cmx = __shfl_sync(0xffffffffu, cmx, ll + 1, 8);
+                                cmy = __shfl_sync(0xffffffffu, cmy, ll + 1, 8);
+                            }
+                        }
+                        const int pc = 16 * cb + 2 * ((ll + 7) & 7);  // the pair finished here
+                        *reinterpret_cast<float2 *>(&S.part[buf][sg][pc]) = make_float2(cmx, cmy);
+                    }
+                    // rows: strict improvement during this superblock => it holds the first minimum
+#pragma unroll
+                    for (int r = 0; r < 8; ++r) {
+                        if (best[r] < prev[r]) {
+                            prev[r] = best[r];
+                            gid[r] = sb0 + sb;
+                            dirty |= 1u << r;
+                        }
+                    }
+                }
+                __syncthreads();
+                // columns: first sub-group (ascending rows, strict '<') holding the minimum.
+                // 4 lanes per column, 8 sub-groups each; part[buf] is rewritten two rounds later,
+                // after the next barrier.
+                {
+                    const int col = t >> 2, q = t & 3;
+                    float bv = inf;
+                    int bs = 0;
+                    const int g1 = min(nsg, 8 * q + 8);
+                    for (int g = 8 * q; g < g1; ++g) {
+                        const float v = S.part[buf][g][col];
+                        if (v < bv) { bv = v; bs = g; }
+                    }
+#pragma unroll
+                    for (int o = 1; o < 4; o <<= 1) {
+                        const float ov = __shfl_xor_sync(0xffffffffu, bv, o);
+                        const int os = __shfl_xor_sync(0xffffffffu, bs, o);
+                        if (ov < bv || (ov == bv && os < bs)) { bv = ov; bs = os; }
+                    }
+                    if (q == 0) {
+                        S.cmin[sb * kSGrp + col] = bv;
+                        S.csg[sb * kSGrp + col] = (unsigned char)bs;
+                    }
+                }
+                buf ^= 1;
+            }
+            __syncthreads();
+
+            // ---- columns of this tile: exact first arg-min among the 64 rows of the winning
+            //      sub-group, then write (single row chunk) or combine across chunks
+            for (int col = t; col < cnt; col += kSThreads) {
+                const float target = S.cmin[col];
+                const int j0 = (int)S.csg[col] * kSGrp;
+                const int bi = first_equal(S.rx, kSRows, j0, S.cx[col], S.cy[col], S.cz[col], target, l);
+                const size_t o = (size_t)b * nc + t0 + col;
+                if (A.keys) {
+                    const unsigned long long key =
+                        ((unsigned long long)__float_as_uint(target) << 32) | (unsigned)(rbase + bi);
+                    atomicMin(A.keys + o, key);
+                } else {
+                    A.dist_c[o] = target;
+                    A.idx_c[o] = rbase + bi;
+                }
+            }
+            // ---- rows improved in this tile: exact first arg-min inside the winning superblock
+            if (scan_active) {
+#pragma unroll
+                for (int r = 0; r < 8; ++r) {
+                    if (dirty & (1u << r)) {
+                        const int j0 = (gid[r] - sb0) * kSGrp;
+                        idxr[r] = t0 + first_equal(S.cx, kSTile, j0, -nqx[r], -nqy[r], -nqz[r], best[r], l);
+                    }
+                }
+            }
+        }
+
+        // ---- row results
+#pragma unroll
+        for (int r = 0; r < 8; ++r) {
+            const int i = row0 + r;
+            if (i < nrows) {
+                A.dist_r[(size_t)b * nr + rbase + i] = best[r];
+                A.idx_r[(size_t)b * nr + rbase + i] = idxr[r];
+            }
+        }
+    }
+}
+
+__global__ void chamfer_sym_unpack(const unsigned long long *keys, float *dist, int *idx, size_t n) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) {
+        const unsigned long long k = keys[i];
+        dist[i] = __uint_as_float((unsigned)(k >> 32));
+        idx[i] = (int)(unsigned)(k & 0xffffffffull);
+    }
+}
+
+// Launch the symmetric forward with `rows` = the cloud chunked over CTAs.  keys: workspace of
+// B*nc 64-bit words, required when nr > kSRows.
+int launch_chamfer_sym(const SymArgs &a, cudaStream_t st) {
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(chamfer_sym_kernel<8>,
+                                             cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             (int)sizeof(SmemK1s));
+        if (e != cudaSuccess) return (int)e;
+        attr_set = true;
+    }
+    const int chunks = (a.nr + kSRows - 1) / kSRows;
+    if (chunks > 1) {
+        if (!a.keys) return HOUV_E_BADARG;
+        cudaError_t e = cudaMemsetAsync(a.keys, 0xff, sizeof(unsigned long long) * (size_t)a.B * a.nc, st);
+        if (e != cudaSuccess) return (int)e;
+    }
+    SymArgs k = a;
+    if (chunks == 1) k.keys = nullptr;
+    dim3 grid(chunks, a.B < 65535 ? a.B : 65535);
+    chamfer_sym_kernel<8><<<grid, kSThreads, sizeof(SmemK1s), st>>>(k);
+    if (int e = check_launch()) return e;
+    if (chunks > 1) {
+        const size_t n = (size_t)a.B * a.nc;
+        chamfer_sym_unpack<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(a.keys, a.dist_c, a.idx_c, n);
+        return check_launch();
+    }
+    return 0;
+}
+
+}  // namespace houv

@@ -37,6 +37,21 @@ __device__ __forceinline__ float2 sqdist2(float2 tx, float2 ty, float2 tz, float
     return __ffma2_rn(dz, dz, __ffma2_rn(dx, dx, __fmul2_rn(dy, dy)));
 }
 
+// Arguments of the symmetric Chamfer forward (chamfer_sym.cu), launched from chamfer_fwd.cu.
+struct SymArgs {
+    const float *rows;   // [B,nr,3]
+    const float *cols;   // [B,nc,3]
+    float *dist_r;       // [B,nr]
+    int *idx_r;          // [B,nr]  index into cols
+    float *dist_c;       // [B,nc]
+    int *idx_c;          // [B,nc]  index into rows
+    unsigned long long *keys;  // [B,nc] workspace when gridDim.x > 1, else null
+    int B, nr, nc;
+};
+
+constexpr int kSymChunkRows = 2048;  // rows of `rows` handled by one CTA
+int launch_chamfer_sym(const SymArgs &a, cudaStream_t st);
+
 inline int check_launch() {
     cudaError_t e = cudaGetLastError();
     return e == cudaSuccess ? 0 : (int)e;

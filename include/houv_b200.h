@@ -24,6 +24,8 @@
 #ifndef HOUV_B200_H
 #define HOUV_B200_H
 
+#include <stddef.h>
+
 #ifdef __cplusplus
 extern "C" {
 #endif
@@ -44,6 +46,16 @@ const char *houv_version(void);
  * outputs, which is what the reference's zero-initialised buffers end up as. */
 int houv_chamfer3d_forward(const float *xyz1, const float *xyz2, int B, int N, int M,
                            float *dist1, float *dist2, int *idx1, int *idx2, void *stream);
+
+/* The same with a caller-provided scratch buffer.  With it the library may pick the symmetric
+ * kernel (csrc/chamfer_sym.cu: every distance evaluated once for both directions) also when the
+ * larger cloud has more than 2048 points; results are identical bit for bit either way.
+ * workspace: device memory of at least houv_chamfer3d_workspace_bytes(B,N,M) bytes, 8-byte
+ * aligned (may be NULL when that is 0); its contents are scratch. */
+size_t houv_chamfer3d_workspace_bytes(int B, int N, int M);
+int houv_chamfer3d_forward_ws(const float *xyz1, const float *xyz2, int B, int N, int M,
+                              float *dist1, float *dist2, int *idx1, int *idx2,
+                              void *workspace, size_t workspace_bytes, void *stream);
 
 /* One directed search: query[B,N,3] against target[B,M,3] -> dist[B,N], idx[B,N]. */
 int houv_nn_search(const float *query, const float *target, int B, int N, int M,
@@ -109,8 +121,9 @@ int houv_icp(const float *src, const float *tgt, int P, int N, int M, const floa
              int init_per_pair, float max_distance, int max_iteration, double relative_fitness,
              double relative_rmse, float *T_out, float *stats, void *stream);
 
-/* Tuning knob for the NN kernel shape: variant 0..3 = (queries/thread, threads/CTA)
- * (2,128) (4,128) (4,64) (2,256); -1 = built-in default.  Returns the old value. */
+/* Tuning knob for the NN kernel: variant 0..3 = two directed scans with (queries/thread,
+ * threads/CTA) (2,128) (4,128) (4,64) (2,256); 10 = the symmetric kernel whenever its workspace
+ * requirement is met; -1 = automatic (symmetric when it fills the GPU).  Returns the old value. */
 int houv_set_nn_variant(int variant);
 
 /* Tuning knob for the K3 scan shape (queries/thread, 8-target halves per arg-min group,

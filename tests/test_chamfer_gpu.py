@@ -13,6 +13,17 @@ from tests.util import grouped, load_npz
 pytestmark = pytest.mark.gpu
 
 
+@pytest.fixture(autouse=True, params=[-1, 10], ids=["k1-auto", "k1-symmetric"])
+def nn_variant(request):
+    """Every test runs with the automatic kernel choice and with the symmetric kernel
+    (csrc/chamfer_sym.cu) forced, whatever the shape."""
+    from houv_b200 import _lib
+    lib = _lib.load()
+    lib.houv_set_nn_variant(request.param)
+    yield request.param
+    lib.houv_set_nn_variant(-1)
+
+
 def _dev(a):
     return torch.from_numpy(np.ascontiguousarray(a)).cuda()
 
@@ -66,6 +77,18 @@ def test_all_kernel_variants(variant):
         _check_fwd(x1, x2)
     finally:
         _lib.load().houv_set_nn_variant(old)
+
+
+@pytest.mark.parametrize("shape", [(3, 4500, 2300), (2, 2300, 4500), (5, 2048, 64), (2, 130, 2050)])
+def test_ties_across_chunks_and_tiles(shape):
+    """Grid-quantised coordinates (many exactly equal distances) with clouds spanning several
+    2048-row chunks / 2048-column tiles of the symmetric kernel and several 512-tiles of the
+    reference: the first minimum must win across every boundary."""
+    b, n, m = shape
+    rng = np.random.RandomState(n + m)
+    x1 = (rng.randint(0, 12, size=(b, n, 3)) / 8.0).astype(np.float32)
+    x2 = (rng.randint(0, 12, size=(b, m, 3)) / 8.0).astype(np.float32)
+    _check_fwd(x1, x2)
 
 
 def test_unaligned_views_and_noncontiguous_inputs():

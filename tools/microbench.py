@@ -67,7 +67,7 @@ def cmd_chamfer():
         d2 = torch.empty(B, M, device="cuda")
         i1 = torch.empty(B, N, device="cuda", dtype=torch.int32)
         i2 = torch.empty(B, M, device="cuda", dtype=torch.int32)
-        for variant in (0, 1, 2, 3):
+        for variant in (0, 1, 10):
             lib.houv_set_nn_variant(variant)
             med, best = timeit(lambda: chamfer_3D.forward(x1, x2, d1, d2, i1, i2), flush=flush)
             evals = 2.0 * B * N * M
