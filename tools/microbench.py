@@ -86,6 +86,46 @@ def cmd_chamfer():
                           "GBps": round(byts / med / 1e6, 1)}))
 
 
+def cmd_refext():
+    """The reference's own CUDA extension (oracle/_ref/chamfer_3D.so, unmodified, sm_100a) beside
+    K1/K2 on the same GPU: forward, backward, and forward as the reference WRAPPER runs it
+    (four CPU zero tensors copied to the device per call, dist_chamfer_3D.py:33-42)."""
+    from oracle import ref_ext
+    from houv_b200.chamfer import chamfer_3D
+    ref = ref_ext.load()
+    flush = torch.zeros(64 * 1024 * 1024, device="cuda")
+    for name, (B, N, M) in {"C2": (32, 2048, 2048), "C5": (64, 16384, 2048),
+                            "unit_timing": (32, 2000, 1000),
+                            "rows6400": (6400, 2048, 2048)}.items():
+        torch.manual_seed(0)
+        x1 = torch.rand(B, N, 3, device="cuda")
+        x2 = torch.rand(B, M, 3, device="cuda")
+        d1 = torch.zeros(B, N, device="cuda"); d2 = torch.zeros(B, M, device="cuda")
+        i1 = torch.zeros(B, N, device="cuda", dtype=torch.int32)
+        i2 = torch.zeros(B, M, device="cuda", dtype=torch.int32)
+        gd1, gd2 = torch.rand(B, N, device="cuda"), torch.rand(B, M, device="cuda")
+        g1, g2 = torch.zeros_like(x1), torch.zeros_like(x2)
+        n_it = 5 if B > 1000 else 20
+
+        def ref_wrapper_fwd():
+            a = torch.zeros(B, N).to("cuda"); b = torch.zeros(B, M).to("cuda")
+            c = torch.zeros(B, N).type(torch.IntTensor).to("cuda")
+            d = torch.zeros(B, M).type(torch.IntTensor).to("cuda")
+            ref.forward(x1, x2, a, b, c, d)
+        rf, _ = timeit(lambda: ref.forward(x1, x2, d1, d2, i1, i2), iters=n_it, flush=flush)
+        rb, _ = timeit(lambda: ref.backward(x1, x2, g1, g2, gd1, gd2, i1, i2), iters=n_it, flush=flush)
+        rw, _ = timeit(ref_wrapper_fwd, iters=n_it, flush=flush)
+        of, _ = timeit(lambda: chamfer_3D.forward(x1, x2, d1, d2, i1, i2), iters=n_it, flush=flush)
+        ob, _ = timeit(lambda: chamfer_3D.backward(x1, x2, g1, g2, gd1, gd2, i1, i2), iters=n_it, flush=flush)
+        print(json.dumps({"case": name, "ref_fwd_ms": round(rf, 4), "ref_bwd_ms": round(rb, 4),
+                          "ref_wrapper_fwd_ms": round(rw, 4), "ours_fwd_ms": round(of, 4),
+                          "ours_bwd_ms": round(ob, 4), "fwd_speedup": round(rf / of, 2),
+                          "bwd_speedup": round(rb / ob, 2),
+                          "fwd_bwd_speedup": round((rf + rb) / (of + ob), 2),
+                          "ref_Gpts2_per_s": round(2.0 * B * N * M / rf / 1e6, 1),
+                          "ours_Gpts2_per_s": round(2.0 * B * N * M / of / 1e6, 1)}))
+
+
 def cmd_pose():
     """K3 at the BASELINE shape: P pairs x 64 starts x `iters` iterations, 2048 points."""
     import numpy as np
@@ -123,4 +163,4 @@ def cmd_pose():
 
 
 if __name__ == "__main__":
-    {"probe": cmd_probe, "chamfer": cmd_chamfer, "pose": cmd_pose}[sys.argv[1] if len(sys.argv) > 1 else "probe"]()
+    {"probe": cmd_probe, "chamfer": cmd_chamfer, "pose": cmd_pose, "refext": cmd_refext}[sys.argv[1] if len(sys.argv) > 1 else "probe"]()
