@@ -12,6 +12,26 @@ _vp = ctypes.c_void_p
 _ci = ctypes.c_int
 _cf = ctypes.c_float
 
+_fp = ctypes.c_void_p  # device pointers travel as integers
+
+
+class HouvPoseProblem(ctypes.Structure):
+    """include/houv_b200.h: struct HouvPoseProblem (same field order)."""
+    _fields_ = [("src", _fp), ("tgt", _fp),
+                ("P", _ci), ("N", _ci), ("M", _ci), ("K", _ci),
+                ("params", _fp), ("adam_m", _fp), ("adam_v", _fp),
+                ("params64", _fp), ("adam_m64", _fp), ("adam_v64", _fp),
+                ("step0", _ci), ("iters", _ci), ("angle_base", _ci),
+                ("lr", ctypes.c_double), ("beta1", ctypes.c_double), ("beta2", ctypes.c_double),
+                ("eps", ctypes.c_double),
+                ("grad_scale", _cf), ("percent", _cf), ("w3d", _cf), ("wview", _cf),
+                ("tran_scale", _cf), ("tran_offset", _cf),
+                ("min1_out", _fp), ("loss_out", _fp), ("R_out", _fp), ("T_out", _fp),
+                ("tran_s_out", _fp), ("trace", _fp),
+                ("row_pair", _fp), ("row_base", _fp),
+                ("rows", _ci)]
+
+
 # name -> argtypes; every entry point returns int (0 = ok) unless noted
 _SIGNATURES = {
     "houv_chamfer3d_forward": [_vp, _vp, _ci, _ci, _ci, _vp, _vp, _vp, _vp, _vp],
@@ -27,6 +47,7 @@ _SIGNATURES = {
     "houv_pose_optimise": [_vp, _vp, _ci, _ci, _ci, _ci, _vp, _vp, _vp, _ci, _ci, _ci,
                            _cf, _cf, _cf, _cf, _cf, _cf, _cf, _cf, _vp, _vp, _vp, _vp, _vp, _vp, _vp,
                            _ci, _vp],
+    "houv_pose_optimise_ex": [ctypes.POINTER(HouvPoseProblem), _vp],
     "houv_fp32_probe": [_vp, _ci, _ci, ctypes.POINTER(ctypes.c_double), _vp],
 }
 

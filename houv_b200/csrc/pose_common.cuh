@@ -25,7 +25,15 @@ struct PoseArgs {
     const int *row_base;  // [rows] angle_base of each row, or null (= angle_base)
     int P, N, M, K, rows;
     int step0, iters, angle_base, k3d;
-    float lr, beta1, beta2, eps, grad_scale, w3d, wview;
+    double lr, beta1, beta2, eps;  // Adam; rounded to float for float32 state as torch does
+    float grad_scale, w3d, wview;
+    // |T| = sin(tran_s*pi)*tran_scale + tran_offset: 0.125/0.125 in houv.py:99, 1/0 in
+    // train_utils.getPredict_angle (train_utils.py:405)
+    float tran_scale, tran_offset;
+    // float64 parameters and Adam moments (getPredict_angle keeps float64 leaves on the host and
+    // feeds their float32 roundings to the forward, train_utils.py:382-401); null = float32 state
+    double *params64, *adam_m64, *adam_v64;
+    float *tran_s_out;  // [rows] |T| of the last forward, or null
 };
 
 // squared distance of metric m between (tx,ty,tz) and (qx,qy,qz), scalar, same
@@ -58,12 +66,14 @@ __device__ __forceinline__ float2 metric_dist2(int m, float2 tx, float2 ty, floa
 
 // Per-row optimiser state, live in thread 0's registers for the whole kernel.
 struct PoseState {
+    double pd[8], md[8], vd[8];  // float64 state (only with PoseArgs::params64)
     float p[8], m[8], v[8];
     // forward intermediates kept for the closed-form backward
     float vh[3], n, A[3][3], A2[3][3], sa, ca, ang, u[3], nt, st;
 };
 
-__device__ __forceinline__ void pose_forward(PoseState &s, float boff, float *pose /*smem[12]*/) {
+__device__ __forceinline__ void pose_forward(PoseState &s, float boff, float tran_scale,
+                                             float tran_offset, float *pose /*smem[12]*/) {
     const float pi = 3.14159274101257324f;  // float32 pi = acos(0)*2, houv.py:19
     // angle = sin(angle_c*pi)*pi/8 + pi/8 + angle_base*pi/4            houv.py:96
     s.ang = __fadd_rn(__fadd_rn(__fmul_rn(sinf(__fmul_rn(s.p[3], pi)), pi) / 8.f, pi / 8.f), boff);
@@ -92,7 +102,8 @@ __device__ __forceinline__ void pose_forward(PoseState &s, float boff, float *po
             pose[i * 3 + j] = __fadd_rn(__fadd_rn(i == j ? 1.f : 0.f, __fmul_rn(s.sa, A[i][j])),
                                         __fmul_rn(omc, s.A2[i][j]));
     // T = tran_c/|tran_c| * (sin(tran_s*pi)*0.125 + 0.125)               houv.py:88-100
-    s.st = __fadd_rn(__fmul_rn(sinf(__fmul_rn(s.p[7], pi)), 0.125f), 0.125f);
+    // (x*1 + 0 is exact, so scale 1 / offset 0 gives train_utils.py:405's sin(tran_s*pi)*1)
+    s.st = __fadd_rn(__fmul_rn(sinf(__fmul_rn(s.p[7], pi)), tran_scale), tran_offset);
     s.nt = sqrtf(__fadd_rn(__fadd_rn(__fmul_rn(s.p[4], s.p[4]), __fmul_rn(s.p[5], s.p[5])),
                            __fmul_rn(s.p[6], s.p[6])));
 #pragma unroll
@@ -104,7 +115,8 @@ __device__ __forceinline__ void pose_forward(PoseState &s, float boff, float *po
 
 // Closed-form chain from dL/dR (GR), dL/dT (gT) to the 8 scalars.
 __device__ __forceinline__ void pose_backward(const PoseState &s, const float (&GR)[3][3],
-                                              const float (&gT)[3], float (&g)[8]) {
+                                              const float (&gT)[3], float tran_scale,
+                                              float (&g)[8]) {
     const float pi = 3.14159274101257324f;
     float dA = 0.f, dA2 = 0.f;
 #pragma unroll
@@ -135,23 +147,72 @@ __device__ __forceinline__ void pose_backward(const PoseState &s, const float (&
     const float udot = gs * s.st;  // u . (gT * st)
 #pragma unroll
     for (int i = 0; i < 3; ++i) g[4 + i] = (gT[i] * s.st - s.u[i] * udot) / s.nt;
-    g[7] = gs * 0.125f * cosf(s.p[7] * pi) * pi;
+    g[7] = gs * tran_scale * cosf(s.p[7] * pi) * pi;
 }
 
-// torch.optim.Adam, default betas/eps, no weight decay / amsgrad (houv.py:118)
+// torch.optim.Adam, no weight decay / amsgrad (houv.py:118, train_utils.py:390): bias corrections
+// from the double hyper-parameters; the element-wise update in the precision of the state.
 __device__ __forceinline__ void adam_step(PoseState &s, const float (&g)[8], const PoseArgs &A,
                                           double &b1t, double &b2t) {
-    b1t *= (double)A.beta1;
-    b2t *= (double)A.beta2;
-    const float step_size = (float)((double)A.lr / (1.0 - b1t));
+    b1t *= A.beta1;
+    b2t *= A.beta2;
+    if (A.params64) {  // float64 leaves: gradients arrive as float32 and are widened exactly
+        const double step_size = A.lr / (1.0 - b1t);
+        const double bc2_sqrt = sqrt(1.0 - b2t);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const double gi = (double)g[i];
+            s.md[i] = s.md[i] * A.beta1 + (1.0 - A.beta1) * gi;
+            s.vd[i] = s.vd[i] * A.beta2 + (1.0 - A.beta2) * gi * gi;
+            const double denom = sqrt(s.vd[i]) / bc2_sqrt + A.eps;
+            s.pd[i] = s.pd[i] - step_size * (s.md[i] / denom);
+            s.p[i] = (float)s.pd[i];  // .float() of the leaf, train_utils.py:397-401
+        }
+        return;
+    }
+    const float step_size = (float)(A.lr / (1.0 - b1t));
     const float bc2_sqrt = (float)sqrt(1.0 - b2t);
-    const float omb1 = (float)(1.0 - (double)A.beta1), omb2 = (float)(1.0 - (double)A.beta2);
+    const float beta1 = (float)A.beta1, beta2 = (float)A.beta2, eps = (float)A.eps;
+    const float omb1 = (float)(1.0 - A.beta1), omb2 = (float)(1.0 - A.beta2);
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
-        s.m[i] = __fadd_rn(__fmul_rn(s.m[i], A.beta1), __fmul_rn(omb1, g[i]));
-        s.v[i] = __fadd_rn(__fmul_rn(s.v[i], A.beta2), __fmul_rn(omb2, __fmul_rn(g[i], g[i])));
-        const float denom = __fadd_rn(sqrtf(s.v[i]) / bc2_sqrt, A.eps);
+        s.m[i] = __fadd_rn(__fmul_rn(s.m[i], beta1), __fmul_rn(omb1, g[i]));
+        s.v[i] = __fadd_rn(__fmul_rn(s.v[i], beta2), __fmul_rn(omb2, __fmul_rn(g[i], g[i])));
+        const float denom = __fadd_rn(sqrtf(s.v[i]) / bc2_sqrt, eps);
         s.p[i] = __fsub_rn(s.p[i], __fmul_rn(step_size, s.m[i] / denom));
+    }
+}
+
+// load / store of the per-row state (thread 0)
+__device__ __forceinline__ void state_load(PoseState &st, const PoseArgs &A, int row) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        if (A.params64) {
+            st.pd[i] = A.params64[(size_t)row * 8 + i];
+            st.md[i] = A.adam_m64 ? A.adam_m64[(size_t)row * 8 + i] : 0.0;
+            st.vd[i] = A.adam_v64 ? A.adam_v64[(size_t)row * 8 + i] : 0.0;
+            st.p[i] = (float)st.pd[i];
+            st.m[i] = 0.f; st.v[i] = 0.f;
+        } else {
+            st.p[i] = A.params[(size_t)row * 8 + i];
+            st.m[i] = A.adam_m ? A.adam_m[(size_t)row * 8 + i] : 0.f;
+            st.v[i] = A.adam_v ? A.adam_v[(size_t)row * 8 + i] : 0.f;
+        }
+    }
+}
+__device__ __forceinline__ void state_store(const PoseState &st, const PoseArgs &A, int row) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        if (A.params64) {
+            A.params64[(size_t)row * 8 + i] = st.pd[i];
+            if (A.adam_m64) A.adam_m64[(size_t)row * 8 + i] = st.md[i];
+            if (A.adam_v64) A.adam_v64[(size_t)row * 8 + i] = st.vd[i];
+            if (A.params) A.params[(size_t)row * 8 + i] = st.p[i];
+        } else {
+            A.params[(size_t)row * 8 + i] = st.p[i];
+            if (A.adam_m) A.adam_m[(size_t)row * 8 + i] = st.m[i];
+            if (A.adam_v) A.adam_v[(size_t)row * 8 + i] = st.v[i];
+        }
     }
 }
 

@@ -45,7 +45,7 @@ struct Smem {
     float red[kThreads / 32][16];
     float pose[12];                       // R (row-major 9) + T (3)
     unsigned selu[8];                     // radix-select broadcast: prefix, rank, tie count
-    float state[96];                      // PoseState of this row (touched by thread 0 only)
+    double state[80];                     // PoseState of this row (touched by thread 0 only)
     double bt[2];                         // beta1^t, beta2^t
 };
 
@@ -172,14 +172,9 @@ __global__ void __launch_bounds__(kThreads, 2) pose_kernel(const PoseArgs A) {
     PoseState &st = *reinterpret_cast<PoseState *>(S.state);
     double &b1t = S.bt[0], &b2t = S.bt[1];
     if (t == 0) {
-#pragma unroll
-        for (int i = 0; i < 8; ++i) {
-            st.p[i] = A.params[(size_t)row * 8 + i];
-            st.m[i] = A.adam_m ? A.adam_m[(size_t)row * 8 + i] : 0.f;
-            st.v[i] = A.adam_v ? A.adam_v[(size_t)row * 8 + i] : 0.f;
-        }
-        b1t = pow((double)A.beta1, (double)A.step0);
-        b2t = pow((double)A.beta2, (double)A.step0);
+        state_load(st, A, row);
+        b1t = pow(A.beta1, (double)A.step0);
+        b2t = pow(A.beta2, (double)A.step0);
     }
     // angle_base*pi/4 evaluated in double and rounded once, as python does (houv.py:96)
     const int abase = A.row_base ? A.row_base[row] : A.angle_base;
@@ -188,7 +183,7 @@ __global__ void __launch_bounds__(kThreads, 2) pose_kernel(const PoseArgs A) {
 
     for (int it = 0; it < A.iters; ++it) {
         // ---- (a) pose from the 8 scalars
-        if (t == 0) pose_forward(st, boff, S.pose);
+        if (t == 0) pose_forward(st, boff, A.tran_scale, A.tran_offset, S.pose);
         __syncthreads();
         float Rm[9], Tv[3];
 #pragma unroll
@@ -346,6 +341,7 @@ __global__ void __launch_bounds__(kThreads, 2) pose_kernel(const PoseArgs A) {
                 for (int i = 0; i < 9; ++i) A.R_out[(size_t)row * 9 + i] = Rm[i];
 #pragma unroll
                 for (int i = 0; i < 3; ++i) A.T_out[(size_t)row * 3 + i] = Tv[i];
+                if (A.tran_s_out) A.tran_s_out[row] = st.st;
             }
         }
 
@@ -356,6 +352,7 @@ __global__ void __launch_bounds__(kThreads, 2) pose_kernel(const PoseArgs A) {
         for (int i = 0; i < 12; ++i) acc[i] = 0.f;
 #pragma unroll
         for (int m = 0; m < 4; ++m) {
+            if (m > 0 && A.wview == 0.f) continue;  // loss = w3d*min_1 only (train_utils.py:439)
             const int dir = side[m];
             const float *qX = dir ? S.yx : S.tx, *qY = dir ? S.yy : S.ty, *qZ = dir ? S.yz : S.tz;
             const float *tX = dir ? S.tx : S.yx, *tY = dir ? S.ty : S.yy, *tZ = dir ? S.tz : S.yz;
@@ -404,21 +401,14 @@ __global__ void __launch_bounds__(kThreads, 2) pose_kernel(const PoseArgs A) {
                 for (int j = 0; j < 3; ++j) GR[i][j] = acc[i * 3 + j];
                 gT[i] = acc[9 + i];
             }
-            pose_backward(st, GR, gT, g);
+            pose_backward(st, GR, gT, A.tran_scale, g);
             adam_step(st, g, A, b1t, b2t);
         }
         // next iteration's (a) is ordered after this by block_sum's barriers + the one below
         __syncthreads();
     }
 
-    if (t == 0) {
-#pragma unroll
-        for (int i = 0; i < 8; ++i) {
-            A.params[(size_t)row * 8 + i] = st.p[i];
-            if (A.adam_m) A.adam_m[(size_t)row * 8 + i] = st.m[i];
-            if (A.adam_v) A.adam_v[(size_t)row * 8 + i] = st.v[i];
-        }
-    }
+    if (t == 0) state_store(st, A, row);
 }
 
 static int g_pose_variant = -1;
@@ -448,33 +438,32 @@ extern "C" int houv_set_pose_variant(int v) {
     return old;
 }
 
-extern "C" int houv_pose_optimise(const float *src, const float *tgt, int P, int N, int M, int K,
-                                  float *params, float *adam_m, float *adam_v, int step0,
-                                  int iters, int angle_base, float lr, float beta1, float beta2,
-                                  float eps, float grad_scale, float percent, float w3d,
-                                  float wview, float *min1_out, float *loss_out, float *R_out,
-                                  float *T_out, float *trace, const int *row_pair,
-                                  const int *row_base, int rows, void *stream) {
-    if (P < 0 || N <= 0 || M <= 0 || K <= 0 || iters < 0 || step0 < 0 || rows < 0)
+extern "C" int houv_pose_optimise_ex(const HouvPoseProblem *q, void *stream) {
+    if (!q) return HOUV_E_BADARG;
+    int rows = q->rows;
+    if (q->P < 0 || q->N <= 0 || q->M <= 0 || q->K <= 0 || q->iters < 0 || q->step0 < 0 || rows < 0)
         return HOUV_E_BADARG;
-    if (rows == 0) rows = P * K;
-    if (rows != P * K && !row_pair) return HOUV_E_BADARG;
-    if (P == 0 || iters == 0 || rows == 0) return 0;
-    if (!src || !tgt || !params || !min1_out || !R_out || !T_out) return HOUV_E_BADARG;
-    if (N > kPts || M > kPts) return HOUV_E_TOOBIG;
+    if (rows == 0) rows = q->P * q->K;
+    if (rows != q->P * q->K && !q->row_pair) return HOUV_E_BADARG;
+    if (q->P == 0 || q->iters == 0 || rows == 0) return 0;
+    if (!q->src || !q->tgt || (!q->params && !q->params64) || !q->min1_out || !q->R_out || !q->T_out)
+        return HOUV_E_BADARG;
+    if (q->N > kPts || q->M > kPts) return HOUV_E_TOOBIG;
     // calc_cd_percent takes k = int(points*percent) from BOTH lists and the view terms use
     // k = N (model_utils_completion.py:85-92); with N != M torch.topk would raise or trim.
-    if (N != M) return HOUV_E_BADARG;
+    if (q->N != q->M) return HOUV_E_BADARG;
     PoseArgs a;
-    a.src = src; a.tgt = tgt; a.params = params; a.adam_m = adam_m; a.adam_v = adam_v;
-    a.min1_out = min1_out; a.loss_out = loss_out; a.R_out = R_out; a.T_out = T_out;
-    a.trace = trace; a.row_pair = row_pair; a.row_base = row_base;
-    a.P = P; a.N = N; a.M = M; a.K = K; a.rows = rows;
-    a.step0 = step0; a.iters = iters; a.angle_base = angle_base;
-    a.k3d = (int)((double)N * (double)percent);
-    if (a.k3d < 1 || a.k3d > N) return HOUV_E_BADARG;
-    a.lr = lr; a.beta1 = beta1; a.beta2 = beta2; a.eps = eps; a.grad_scale = grad_scale;
-    a.w3d = w3d; a.wview = wview;
+    a.src = q->src; a.tgt = q->tgt; a.params = q->params; a.adam_m = q->adam_m; a.adam_v = q->adam_v;
+    a.params64 = q->params64; a.adam_m64 = q->adam_m64; a.adam_v64 = q->adam_v64;
+    a.min1_out = q->min1_out; a.loss_out = q->loss_out; a.R_out = q->R_out; a.T_out = q->T_out;
+    a.tran_s_out = q->tran_s_out; a.trace = q->trace; a.row_pair = q->row_pair; a.row_base = q->row_base;
+    a.P = q->P; a.N = q->N; a.M = q->M; a.K = q->K; a.rows = rows;
+    a.step0 = q->step0; a.iters = q->iters; a.angle_base = q->angle_base;
+    a.k3d = (int)((double)q->N * (double)q->percent);
+    if (a.k3d < 1 || a.k3d > q->N) return HOUV_E_BADARG;
+    a.lr = q->lr; a.beta1 = q->beta1; a.beta2 = q->beta2; a.eps = q->eps;
+    a.grad_scale = q->grad_scale; a.w3d = q->w3d; a.wview = q->wview;
+    a.tran_scale = q->tran_scale; a.tran_offset = q->tran_offset;
     cudaStream_t st = (cudaStream_t)stream;
     if (g_pose_variant < 0) {  // not set through the API: HOUV_POSE_VARIANT, else the default
         const char *e = getenv("HOUV_POSE_VARIANT");
@@ -484,6 +473,8 @@ extern "C" int houv_pose_optimise(const float *src, const float *tgt, int P, int
         case 10: return launch_pose_sym(a, 2, st);
         case 11: return launch_pose_sym(a, 4, st);
         case 12: return launch_pose_sym(a, 8, st);
+        case 13: return launch_pose_sym(a, 84, st);
+        case 14: return launch_pose_sym(a, 44, st);
         case 1: return launch_pose<4, 1, 2>(a, st);
         case 2: return launch_pose<4, 2, 1>(a, st);
         case 3: return launch_pose<2, 1, 2>(a, st);
@@ -492,4 +483,27 @@ extern "C" int houv_pose_optimise(const float *src, const float *tgt, int P, int
         case 0:
         default: return launch_pose<4, 1, 1>(a, st);
     }
+}
+
+extern "C" int houv_pose_optimise(const float *src, const float *tgt, int P, int N, int M, int K,
+                                  float *params, float *adam_m, float *adam_v, int step0,
+                                  int iters, int angle_base, float lr, float beta1, float beta2,
+                                  float eps, float grad_scale, float percent, float w3d,
+                                  float wview, float *min1_out, float *loss_out, float *R_out,
+                                  float *T_out, float *trace, const int *row_pair,
+                                  const int *row_base, int rows, void *stream) {
+    HouvPoseProblem q = {};
+    q.src = src; q.tgt = tgt; q.P = P; q.N = N; q.M = M; q.K = K;
+    q.params = params; q.adam_m = adam_m; q.adam_v = adam_v;
+    q.step0 = step0; q.iters = iters; q.angle_base = angle_base;
+    // the float arguments are roundings of the caller's doubles (0.9f etc.): widen the decimal
+    // value back where it is one of torch's defaults so that 1-beta is what torch computes
+    q.lr = (double)lr; q.beta1 = beta1 == 0.9f ? 0.9 : (double)beta1;
+    q.beta2 = beta2 == 0.999f ? 0.999 : (double)beta2; q.eps = eps == 1e-8f ? 1e-8 : (double)eps;
+    if (lr == 0.01f) q.lr = 0.01;
+    q.grad_scale = grad_scale; q.percent = percent; q.w3d = w3d; q.wview = wview;
+    q.tran_scale = 0.125f; q.tran_offset = 0.125f;  // houv.py:99
+    q.min1_out = min1_out; q.loss_out = loss_out; q.R_out = R_out; q.T_out = T_out;
+    q.trace = trace; q.row_pair = row_pair; q.row_base = row_base; q.rows = rows;
+    return houv_pose_optimise_ex(&q, stream);
 }

@@ -52,7 +52,7 @@ struct SmemSym {
     float red[kSymThreads / 32][16];
     float pose[12];
     unsigned selu[8];
-    float state[96];
+    double state[80];                     // PoseState of this row (touched by thread 0 only)
     double bt[2];
 };
 
@@ -95,28 +95,33 @@ __device__ __forceinline__ void eval4(const float2 X, const float2 Y, const floa
     b = __ffma2_rn(dz, dz, xx);
 }
 
-// One rotation step: 8 rows x one column pair.
+// One rotation step: 8 rows x one column pair, kRG rows evaluated before their folds.
+template <int kRG>
 __device__ __forceinline__ void sym_step(const float2 X, const float2 Y, const float2 Z,
                                          const float (&nqx)[8], const float (&nqy)[8],
                                          const float (&nqz)[8], float (&best)[4][8],
                                          float (&cmx)[4], float (&cmy)[4]) {
 #pragma unroll
-    for (int r = 0; r < 8; r += 2) {
-        float2 v0[4], v1[4];
-        eval4(X, Y, Z, nqx[r], nqy[r], nqz[r], v0[0], v0[1], v0[2], v0[3]);
-        eval4(X, Y, Z, nqx[r + 1], nqy[r + 1], nqz[r + 1], v1[0], v1[1], v1[2], v1[3]);
+    for (int r = 0; r < 8; r += kRG) {
+        float2 v[kRG][4];
+#pragma unroll
+        for (int i = 0; i < kRG; ++i)
+            eval4(X, Y, Z, nqx[r + i], nqy[r + i], nqz[r + i], v[i][0], v[i][1], v[i][2], v[i][3]);
 #pragma unroll
         for (int m = 0; m < 4; ++m) {
-            best[m][r] = min3(best[m][r], v0[m].x, v0[m].y);
-            best[m][r + 1] = min3(best[m][r + 1], v1[m].x, v1[m].y);
-            cmx[m] = min3(cmx[m], v0[m].x, v1[m].x);
-            cmy[m] = min3(cmy[m], v0[m].y, v1[m].y);
+#pragma unroll
+            for (int i = 0; i < kRG; ++i) best[m][r + i] = min3(best[m][r + i], v[i][m].x, v[i][m].y);
+#pragma unroll
+            for (int i = 0; i < kRG; i += 2) {
+                cmx[m] = min3(cmx[m], v[i][m].x, v[i + 1][m].x);
+                cmy[m] = min3(cmy[m], v[i][m].y, v[i + 1][m].y);
+            }
         }
     }
 }
 
 // kSymUnroll: unroll of the 8 rotation steps of a phase
-template <int kSymUnroll>
+template <int kSymUnroll, int kRG>
 __global__ void __launch_bounds__(kSymThreads, 1) pose_sym_kernel(const PoseArgs A) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     SmemSym &S = *reinterpret_cast<SmemSym *>(smem_raw);
@@ -154,14 +159,9 @@ __global__ void __launch_bounds__(kSymThreads, 1) pose_sym_kernel(const PoseArgs
     PoseState &st = *reinterpret_cast<PoseState *>(S.state);
     double &b1t = S.bt[0], &b2t = S.bt[1];
     if (t == 0) {
-#pragma unroll
-        for (int i = 0; i < 8; ++i) {
-            st.p[i] = A.params[(size_t)row * 8 + i];
-            st.m[i] = A.adam_m ? A.adam_m[(size_t)row * 8 + i] : 0.f;
-            st.v[i] = A.adam_v ? A.adam_v[(size_t)row * 8 + i] : 0.f;
-        }
-        b1t = pow((double)A.beta1, (double)A.step0);
-        b2t = pow((double)A.beta2, (double)A.step0);
+        state_load(st, A, row);
+        b1t = pow(A.beta1, (double)A.step0);
+        b2t = pow(A.beta2, (double)A.step0);
     }
     const int abase = A.row_base ? A.row_base[row] : A.angle_base;
     const float boff = (float)((double)abase * 3.14159274101257324 / 4.0);
@@ -173,7 +173,7 @@ __global__ void __launch_bounds__(kSymThreads, 1) pose_sym_kernel(const PoseArgs
 
     for (int it = 0; it < A.iters; ++it) {
         // ---- (a) pose from the 8 scalars
-        if (t == 0) pose_forward(st, boff, S.pose);
+        if (t == 0) pose_forward(st, boff, A.tran_scale, A.tran_offset, S.pose);
         __syncthreads();
         float Rm[9], Tv[3];
 #pragma unroll
@@ -234,7 +234,7 @@ __global__ void __launch_bounds__(kSymThreads, 1) pose_sym_kernel(const PoseArgs
                         const float2 X = *reinterpret_cast<const float2 *>(&S.tx[c]);
                         const float2 Y = *reinterpret_cast<const float2 *>(&S.ty[c]);
                         const float2 Z = *reinterpret_cast<const float2 *>(&S.tz[c]);
-                        sym_step(X, Y, Z, nqx, nqy, nqz, best, cmx, cmy);
+                        sym_step<kRG>(X, Y, Z, nqx, nqy, nqz, best, cmx, cmy);
                         if (s < 7) {  // the column pair moves on to lane ll-1; ours comes from ll+1
 #pragma unroll
                             for (int m = 0; m < 4; ++m) {
@@ -405,6 +405,7 @@ __global__ void __launch_bounds__(kSymThreads, 1) pose_sym_kernel(const PoseArgs
                 for (int i = 0; i < 9; ++i) A.R_out[(size_t)row * 9 + i] = Rm[i];
 #pragma unroll
                 for (int i = 0; i < 3; ++i) A.T_out[(size_t)row * 3 + i] = Tv[i];
+                if (A.tran_s_out) A.tran_s_out[row] = st.st;
             }
         }
 
@@ -418,6 +419,7 @@ __global__ void __launch_bounds__(kSymThreads, 1) pose_sym_kernel(const PoseArgs
         const int lane = t & 31;
 #pragma unroll
         for (int m = 0; m < 4; ++m) {
+            if (m > 0 && A.wview == 0.f) continue;  // loss = w3d*min_1 only (train_utils.py:439)
             const int dir = side[m];
             // x, y, z of a cloud are consecutive kPts-float arrays: one base pointer per cloud
             const float *qB = dir ? S.yx : S.tx, *tB = dir ? S.tx : S.yx;
@@ -472,41 +474,36 @@ __global__ void __launch_bounds__(kSymThreads, 1) pose_sym_kernel(const PoseArgs
                 for (int j = 0; j < 3; ++j) GR[i][j] = acc[i * 3 + j];
                 gT[i] = acc[9 + i];
             }
-            pose_backward(st, GR, gT, g);
+            pose_backward(st, GR, gT, A.tran_scale, g);
             adam_step(st, g, A, b1t, b2t);
         }
         __syncthreads();
     }
 
-    if (t == 0) {
-#pragma unroll
-        for (int i = 0; i < 8; ++i) {
-            A.params[(size_t)row * 8 + i] = st.p[i];
-            if (A.adam_m) A.adam_m[(size_t)row * 8 + i] = st.m[i];
-            if (A.adam_v) A.adam_v[(size_t)row * 8 + i] = st.v[i];
-        }
-    }
+    if (t == 0) state_store(st, A, row);
 }
 
-template <int kU>
+template <int kU, int kRG>
 static int launch_sym(const PoseArgs &a, cudaStream_t st) {
     static bool attr_set = false;
     if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(pose_sym_kernel<kU>,
+        cudaError_t e = cudaFuncSetAttribute(pose_sym_kernel<kU, kRG>,
                                              cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              (int)sizeof(SmemSym));
         if (e != cudaSuccess) return (int)e;
         attr_set = true;
     }
-    pose_sym_kernel<kU><<<a.rows, kSymThreads, sizeof(SmemSym), st>>>(a);
+    pose_sym_kernel<kU, kRG><<<a.rows, kSymThreads, sizeof(SmemSym), st>>>(a);
     return check_launch();
 }
 
 int launch_pose_sym(const PoseArgs &a, int unroll, cudaStream_t st) {
     switch (unroll) {
-        case 4: return launch_sym<4>(a, st);
-        case 8: return launch_sym<8>(a, st);
-        default: return launch_sym<2>(a, st);
+        case 4: return launch_sym<4, 2>(a, st);
+        case 8: return launch_sym<8, 2>(a, st);
+        case 84: return launch_sym<8, 4>(a, st);
+        case 44: return launch_sym<4, 4>(a, st);
+        default: return launch_sym<2, 2>(a, st);
     }
 }
 

@@ -120,21 +120,33 @@ class HOUV(nn.Module):
 def pose_optimise(src, tgt, params, kernel, iters, angle_base=0, grad_scale=None,
                   adam_m=None, adam_v=None, step0=0, lr=ADAM_LR, betas=ADAM_BETAS, eps=ADAM_EPS,
                   percent=ALPHA, w3d=W_3D, wview=W_VIEW, want_loss=False, want_trace=False,
-                  row_pair=None, row_base=None):
-    """Thin wrapper over the C ABI houv_pose_optimise (K3).
-    src[P,N,3], tgt[P,N,3] device float32; params[P*kernel,8] is updated IN PLACE.
+                  row_pair=None, row_base=None, tran_scale=0.125, tran_offset=0.125,
+                  want_tran_s=False):
+    """Thin wrapper over the C ABI houv_pose_optimise_ex (K3).
+    src[P,N,3], tgt[P,N,3] device float32; params[P*kernel,8] is updated IN PLACE: float32
+    (HOUV, houv.py) or float64 (train_utils.getPredict_angle keeps float64 leaves; adam_m /
+    adam_v must then be float64 too).
     row_pair / row_base (int32 device tensors [rows]) optionally map every row to a pair
     and an angle_base of its own; rows is then params.shape[0] instead of P*kernel.
-    -> dict(min_1[rows], R[rows,3,3], T[rows,3], loss[rows]|None, trace[iters,rows,2]|None)"""
+    -> dict(min_1[rows], R[rows,3,3], T[rows,3], loss[rows]|None, trace[iters,rows,2]|None,
+            tran_s[rows]|None)"""
     _lib.require_cuda_f32(src, "src", 3)
     _lib.require_cuda_f32(tgt, "tgt", 3)
-    _lib.require_cuda_f32(params, "params")
+    if not isinstance(params, torch.Tensor) or not params.is_cuda or \
+            params.dtype not in (torch.float32, torch.float64):
+        raise RuntimeError("params must be a float32 or float64 CUDA tensor "
+                           "(houv_b200 has no CPU path)")
+    f64 = params.dtype == torch.float64
     src, tgt = src.contiguous(), tgt.contiguous()
     P, N, _ = src.shape
     M = tgt.shape[1]
     rows = P * kernel if row_pair is None else int(row_pair.shape[0])
     if tuple(params.shape) != (rows, 8) or not params.is_contiguous():
         raise RuntimeError("params must be a contiguous [rows, 8] tensor (rows = P*kernel)")
+    for name, a in (("adam_m", adam_m), ("adam_v", adam_v)):
+        if a is not None and (a.dtype != params.dtype or not a.is_cuda or
+                              tuple(a.shape) != (rows, 8) or not a.is_contiguous()):
+            raise RuntimeError(name + " must match params in dtype, device and shape")
     for name, a in (("row_pair", row_pair), ("row_base", row_base)):
         if a is not None and (a.dtype != torch.int32 or not a.is_cuda or a.numel() != rows
                               or not a.is_contiguous()):
@@ -147,25 +159,36 @@ def pose_optimise(src, tgt, params, kernel, iters, angle_base=0, grad_scale=None
     T = torch.empty(rows, 3, device=dev)
     loss = torch.empty(rows, device=dev) if want_loss else None
     trace = torch.empty(iters, rows, 2, device=dev) if want_trace else None
+    tran_s = torch.empty(rows, device=dev) if want_tran_s else None
     ptr = lambda x: 0 if x is None else x.data_ptr()
     if grad_scale is None:
         grad_scale = 1.0 / rows  # rmse_loss.mean() over every row of the batch, houv.py:124
+    q = _lib.HouvPoseProblem()
+    q.src, q.tgt, q.P, q.N, q.M, q.K = src.data_ptr(), tgt.data_ptr(), P, N, M, kernel
+    if f64:
+        q.params64, q.adam_m64, q.adam_v64 = params.data_ptr(), ptr(adam_m), ptr(adam_v)
+    else:
+        q.params, q.adam_m, q.adam_v = params.data_ptr(), ptr(adam_m), ptr(adam_v)
+    q.step0, q.iters, q.angle_base = step0, iters, int(angle_base)
+    q.lr, q.beta1, q.beta2, q.eps = lr, betas[0], betas[1], eps
+    q.grad_scale, q.percent, q.w3d, q.wview = grad_scale, percent, w3d, wview
+    q.tran_scale, q.tran_offset = tran_scale, tran_offset
+    q.min1_out, q.loss_out, q.R_out, q.T_out = min1.data_ptr(), ptr(loss), R.data_ptr(), T.data_ptr()
+    q.tran_s_out, q.trace = ptr(tran_s), ptr(trace)
+    q.row_pair, q.row_base, q.rows = ptr(row_pair), ptr(row_base), rows
     timing = KERNEL_TIMING
     if timing is not None:
         ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         ev0.record()
+    import ctypes
     with torch.cuda.device(dev):
-        rc = _lib.load().houv_pose_optimise(
-            src.data_ptr(), tgt.data_ptr(), P, N, M, kernel, params.data_ptr(), ptr(adam_m),
-            ptr(adam_v), step0, iters, int(angle_base), lr, betas[0], betas[1], eps,
-            grad_scale, percent, w3d, wview, min1.data_ptr(), ptr(loss), R.data_ptr(),
-            T.data_ptr(), ptr(trace), ptr(row_pair), ptr(row_base), rows, _lib.stream_ptr())
-    _lib.check(rc, "houv_pose_optimise")
+        rc = _lib.load().houv_pose_optimise_ex(ctypes.byref(q), _lib.stream_ptr())
+    _lib.check(rc, "houv_pose_optimise_ex")
     _lib.count_launches(1)
     if timing is not None:
         ev1.record()
         timing.append((ev0, ev1, rows, iters, N))
-    return dict(min_1=min1, R=R, T=T, loss=loss, trace=trace)
+    return dict(min_1=min1, R=R, T=T, loss=loss, trace=trace, tran_s=tran_s)
 
 
 def predict_model(net, src, src_rotated, pose=None, src_ori=None, tgt_ori=None, angle_t=None,

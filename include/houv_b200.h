@@ -101,6 +101,29 @@ int houv_pose_optimise(const float *src, const float *tgt, int P, int N, int M, 
                        float *trace, const int *row_pair, const int *row_base, int rows,
                        void *stream);
 
+/* The same kernel with every knob in a struct (zero-initialise, then fill).  Adds what the older
+ * functional solver of the reference needs -- train_utils.getPredict_angle / solve
+ * (registration/train_utils.py:359-572), the path behind test.py:64: float64 parameters and
+ * Adam state (params64 != NULL: the forward sees their float32 roundings, :397-401),
+ * |T| = sin(tran_s*pi)*tran_scale + tran_offset (1 and 0 at :405; 0.125/0.125 in houv.py:99),
+ * double Adam hyper-parameters (lr 0.1 at :390), wview = 0 (loss 6*min_1 only, :439: the view
+ * terms then take no part in the gradient), and tran_s_out[rows] = |T| of the last forward
+ * (returned by getPredict_angle, :456). */
+typedef struct HouvPoseProblem {
+    const float *src, *tgt;          /* [P,N,3], [P,M,3] */
+    int P, N, M, K;
+    float *params, *adam_m, *adam_v; /* [rows,8] float32 state (HOUV); params may be NULL with params64 */
+    double *params64, *adam_m64, *adam_v64; /* [rows,8] float64 state, or NULL */
+    int step0, iters, angle_base;
+    double lr, beta1, beta2, eps;
+    float grad_scale, percent, w3d, wview;
+    float tran_scale, tran_offset;
+    float *min1_out, *loss_out, *R_out, *T_out, *tran_s_out, *trace;
+    const int *row_pair, *row_base;
+    int rows;                        /* 0 = P*K */
+} HouvPoseProblem;
+int houv_pose_optimise_ex(const HouvPoseProblem *problem, void *stream);
+
 /* Batched Kabsch (K4), SVDHead.forward semantics (model_utils.py:220-255).
  *   src[B,3,N], src_corr[B,3,N]  channel-first clouds, corresponding columns
  *   weights[B,N] or NULL         H = (src_c * w) corr_c^T; means stay unweighted (:221-227),
@@ -126,9 +149,11 @@ int houv_icp(const float *src, const float *tgt, int P, int N, int M, const floa
  * requirement is met; -1 = automatic (symmetric when it fills the GPU).  Returns the old value. */
 int houv_set_nn_variant(int variant);
 
-/* Tuning knob for the K3 scan shape (queries/thread, 8-target halves per arg-min group,
- * unroll): 0 (4,1,1) 1 (4,1,2) 2 (4,2,1) 3 (2,1,2) 4 (2,2,2) 5 (4,2,2); -1 = default.
- * Results are identical for every variant. Returns the old value. */
+/* Tuning knob for K3: 0..5 = the two-directed-scans kernel (csrc/pose_opt.cu) with (queries/
+ * thread, 8-target halves per arg-min group, unroll) (4,1,1) (4,1,2) (4,2,1) (2,1,2) (2,2,2)
+ * (4,2,2), identical results; 10..14 = the symmetric-scan kernel (csrc/pose_sym.cu) with
+ * different unrolls, identical results among themselves and equal to 0..5 up to the summation
+ * order of the loss terms; -1 = default (12, or $HOUV_POSE_VARIANT).  Returns the old value. */
 int houv_set_pose_variant(int variant);
 
 /* FP32 CUDA-core peak probe: runs `iters` x 64 FFMA (or FFMA2 when packed) per thread on a

@@ -5,6 +5,7 @@ HOUV solver:
     registration/models/houv.py:13-222           HOUV, predict_model, solve_model, Predict_loss
     registration/model_utils_completion.py:69-166 calc_cd, calc_cd_percent, loss_view
     registration/train_utils.py:82-95             rotation_error, translation_error, rmse_loss
+    registration/train_utils.py:113-148,359-572   rotation, translation, getPredict_angle, solve
     registration/model_utils.py:213-255           SVDHead
 (paths relative to /root/reference).  The reference files hard-code .cuda() and
 import absent packages, so they cannot run on the GPU box; this restatement can.
@@ -266,6 +267,99 @@ def solve_model(net, src, src_rotated, pose=None, kernel=64, num_epochs=200, pre
 
 
 # ---------------------------------------------------------------- Kabsch head
+# ------------------------------------------------- train_utils.py functional solver
+def tu_rotation(angle, V):
+    """train_utils.py:113-130."""
+    batch_size = angle.shape[0]
+    V = V / torch.sqrt((V * V).sum(dim=1, keepdim=True))
+    A = torch.zeros((batch_size, 3, 3))
+    A[:, 0, 1] = -V[:, 2]
+    A[:, 0, 2] = V[:, 1]
+    A[:, 1, 0] = V[:, 2]
+    A[:, 1, 2] = -V[:, 0]
+    A[:, 2, 0] = -V[:, 1]
+    A[:, 2, 1] = V[:, 0]
+    ones = torch.zeros((batch_size, 3, 3)) + torch.eye(3)
+    return ones + torch.sin(angle).unsqueeze(2) * A + (1 - torch.cos(angle)).unsqueeze(2) * torch.bmm(A, A)
+
+
+def tu_translation(tran, s):
+    """train_utils.py:143-148."""
+    tran = tran / torch.sqrt((tran * tran).sum(dim=1, keepdim=True))
+    return (tran * s).unsqueeze(1)
+
+
+def getPredict_angle(src, src_rotated, kernel=64, num_epochs=1000, angle_base=0, trace=None):
+    """train_utils.py:359-456: float64 leaves drawn from NumPy's global generator, their float32
+    roundings in the forward, Adam(lr=0.1), loss 6*min_1, |T| = sin(tran_s*pi)*1.
+    -> (min_1[B,K], R[B,K,3,3], T[B,K,3], tran_s[B*K,1]) of the last forward.
+    trace (list) receives per iteration dict(loss, min_1, grads[4])."""
+    batch_size, num_points = src.shape[0], src.shape[1]
+    src = src.unsqueeze(1).expand((-1, kernel, -1, -1)).reshape(-1, num_points, 3)
+    src_rotated = src_rotated.unsqueeze(1).expand((-1, kernel, -1, -1)).reshape(-1, num_points, 3)
+    batch_size *= kernel
+    V_c = torch.from_numpy(np.random.randn(batch_size, 3)).requires_grad_()
+    angle_c = torch.from_numpy(np.random.randn(batch_size, 1)).requires_grad_()
+    tran_c = torch.from_numpy(np.random.randn(batch_size, 3)).requires_grad_()
+    tran_s_cpu = torch.from_numpy(np.random.randn(batch_size, 1)).requires_grad_()
+    angle_XYZ_c = torch.from_numpy(np.random.randn(batch_size, 3)).requires_grad_()
+    vari_list = [V_c, angle_c, tran_c, tran_s_cpu, angle_XYZ_c]
+    optimizer = torch.optim.Adam(vari_list, lr=0.1)
+    pi = torch.acos(torch.zeros(1)).item() * 2
+    for i in range(num_epochs):
+        optimizer.zero_grad()
+        V, tran, angle, tran_s = V_c.float(), tran_c.float(), angle_c.float(), tran_s_cpu.float()
+        angle = torch.sin(angle * pi) * pi / 8 + pi / 8 + angle_base * pi / 4
+        tran_s = torch.sin(tran_s * pi) * 1
+        R = tu_rotation(angle, V)
+        T = tu_translation(tran, tran_s)
+        src_temp = torch.bmm(src, R.transpose(1, 2)) + T
+        cd_t, cd_p = calc_cd_percent(src_temp, src_rotated, percent=0.5)
+        min_1, _ = torch.min(torch.cat([cd_t.unsqueeze(1), cd_p.unsqueeze(1)], dim=1), dim=1)
+        rmse_loss_ = min_1 * 6
+        rmse_loss_.mean().backward()
+        if trace is not None:
+            trace.append(dict(loss=rmse_loss_.detach().clone(), min_1=min_1.detach().clone(),
+                              grads=[p.grad.detach().clone() for p in vari_list[:4]]))
+        optimizer.step()
+    batch_size = batch_size // kernel
+    return (min_1.reshape((batch_size, kernel)), R.reshape((batch_size, kernel, 3, 3)),
+            T.reshape((batch_size, kernel, 3)), tran_s)
+
+
+def solve(src, src_rotated, pose=None, kernel=64, epochs=500, prefix='train', threshold=0.030):
+    """train_utils.py:467-572 (angle_num = 1).  `epochs` stands for the literal 500 the reference
+    passes to getPredict_angle (:488, :503)."""
+    batch_size = src.shape[0]
+    rmse_loss_, R, T, _ = getPredict_angle(src, src_rotated, kernel=kernel, num_epochs=epochs,
+                                           angle_base=0)
+    rmse_loss_, R, T = rmse_loss_.detach().clone(), R.detach().clone(), T.detach().clone()
+    rmse, _ = rmse_loss_.topk(1, dim=1, largest=False, sorted=True)
+    lst_add = [j for j in range(batch_size) if rmse[j][0] > threshold]
+    if len(lst_add) >= 1:
+        src_add, src_rotated_add = src[lst_add], src_rotated[lst_add]
+        lst_add = np.array(lst_add).astype(int)
+        for base_angle in range(1, 4):
+            rmse_loss_add, R_add, T_add, _ = getPredict_angle(src_add, src_rotated_add, kernel=kernel,
+                                                              num_epochs=epochs, angle_base=base_angle)
+            rmse_add, _ = rmse_loss_add.detach().topk(1, dim=1, largest=False, sorted=True)
+            flag = torch.nonzero((rmse_add < rmse[lst_add]).reshape(-1)).reshape(-1)
+            geid = lst_add[flag.int().numpy()]
+            R[geid] = R_add.detach()[flag]
+            rmse_loss_[geid] = rmse_loss_add.detach()[flag]
+            T[geid] = T_add.detach()[flag]
+            rmse[geid] = rmse_add[flag]
+    ans = torch.zeros((batch_size, 4, 4))
+    for i in range(batch_size):
+        _, idx = rmse_loss_[i].topk(1, dim=0, largest=False, sorted=True)
+        ans[i, :3, :3] = R[i][idx]
+        ans[i, :3, 3] = T[i][idx]
+    if prefix == 'test':
+        return ans
+    return (rotation_error(ans[:, :3, :3], pose[:, :3, :3]),
+            translation_error(ans[:, :3, 3], pose[:, :3, 3]), ans)
+
+
 class SVDHead(nn.Module):
     """registration/model_utils.py:213-255, restated verbatim in behaviour (per-sample
     torch.svd loop, reflection fix, weighted translation)."""

@@ -125,6 +125,40 @@ def make_houv():
     print("houv fixtures written")
 
 
+def make_solve():
+    """solve_ref.npz: the reference's OWN train_utils.getPredict_angle / solve
+    (registration/train_utils.py:359-572, unmodified) on small synthetic pairs with NumPy seeded
+    just before each call.  solve() passes the literal 500 to getPredict_angle (:488, :503); the
+    fixture intercepts that inner call to shorten the horizon -- solve's own code runs as is."""
+    import torch
+    import ref_loader
+    from houv_b200 import synth
+    tu = ref_loader.load()["tu"]
+    s, t, tr = synth.make_pairs(200, 3, n_points=128)
+    src, tgt, gt = torch.from_numpy(s), torch.from_numpy(t), torch.from_numpy(tr)
+    out = dict(src=s, tgt=t, transform=tr)
+    for base, its in ((0, 1), (0, 4), (2, 4)):
+        np.random.seed(77)
+        l, R, T, ts = tu.getPredict_angle(src, tgt, kernel=16, num_epochs=its, angle_base=base)
+        k = "gpa_b%d_i%d_" % (base, its)
+        out[k + "min_1"], out[k + "R"] = l.detach().numpy(), R.detach().numpy()
+        out[k + "T"], out[k + "tran_s"] = T.detach().numpy(), ts.detach().numpy()
+    orig = tu.getPredict_angle
+    tu.getPredict_angle = lambda *a, **k: orig(*a, **dict(k, num_epochs=6))
+    try:
+        np.random.seed(78)
+        # prefix='test' is how test.py:64 calls it (the 'train' branch plots pairs above 70 deg
+        # through matplotlib, train_utils.py:556-562)
+        ans = tu.solve(src, tgt, gt, kernel=16, prefix='test')
+    finally:
+        tu.getPredict_angle = orig
+    out.update(solve_ans=ans.detach().numpy(),
+               solve_r_err=tu.rotation_error(ans[:, :3, :3].detach(), gt[:, :3, :3]).numpy(),
+               solve_t_err=tu.translation_error(ans[:, :3, 3].detach(), gt[:, :3, 3]).numpy())
+    np.savez_compressed(os.path.join(HERE, "solve_ref.npz"), **out)
+    print("solve fixtures written")
+
+
 def make_svd():
     """svdhead_ref.npz: the reference's SVDHead class (model_utils.py:213-255, source read
     and executed as-is) on noisy rigid correspondences, with and without weights, including
@@ -152,7 +186,7 @@ def make_svd():
     print("svd fixtures written")
 
 
-FAMILIES = {"chamfer": make_chamfer, "houv": make_houv, "svd": make_svd}
+FAMILIES = {"chamfer": make_chamfer, "houv": make_houv, "svd": make_svd, "solve": make_solve}
 
 if __name__ == "__main__":
     want = sys.argv[1:] or list(FAMILIES)

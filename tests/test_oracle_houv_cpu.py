@@ -81,3 +81,30 @@ def test_icp_oracle_recovers_small_motion():
     T, fit, rm, it = oh.icp_point_to_point(src, tgt, max_distance=0.05, max_iteration=100)
     assert fit == 1.0 and rm < 1e-6 and it < 100
     assert np.abs(T[:3, :3] - Rz).max() < 1e-6
+
+
+# ---------------------------------------------------------------- train_utils.py solver
+def test_getPredict_angle_matches_reference_golden():
+    """oracle getPredict_angle vs the reference's own (train_utils.py:359-456), NumPy seeded the
+    same way: float64 leaves, lr 0.1, loss 6*min_1, |T| = sin(tran_s*pi)."""
+    g = load_npz("solve_ref.npz")
+    src, tgt = torch.from_numpy(g["src"]), torch.from_numpy(g["tgt"])
+    for base, its in ((0, 1), (0, 4), (2, 4)):
+        np.random.seed(77)
+        l, R, T, ts = oh.getPredict_angle(src, tgt, kernel=16, num_epochs=its, angle_base=base)
+        k = "gpa_b%d_i%d_" % (base, its)
+        assert _close(l.detach(), g[k + "min_1"], 1e-5) and _close(R.detach(), g[k + "R"], 1e-5)
+        assert _close(T.detach(), g[k + "T"], 1e-5) and _close(ts.detach(), g[k + "tran_s"], 1e-5)
+
+
+def test_solve_matches_reference_golden():
+    """oracle solve vs the reference's own solve (train_utils.py:467-572) with its inner
+    500-iteration calls shortened to 6: all three pairs stay above 0.030 and go through the
+    angle_base 1..3 retries, each drawing fresh values from NumPy's global generator."""
+    g = load_npz("solve_ref.npz")
+    src, tgt, gt = (torch.from_numpy(g[k]) for k in ("src", "tgt", "transform"))
+    np.random.seed(78)
+    r_err, t_err, ans = oh.solve(src, tgt, gt, kernel=16, epochs=6)
+    assert _close(ans, g["solve_ans"], 1e-4)
+    assert np.abs(ans[:, 3].numpy()).max() == 0
+    assert _close(r_err, g["solve_r_err"], 1e-3) and _close(t_err, g["solve_t_err"], 1e-4)

@@ -9,6 +9,7 @@ import json
 import os
 import sys
 
+import numpy as np
 import torch
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
@@ -126,6 +127,35 @@ def cmd_refext():
                           "ours_Gpts2_per_s": round(2.0 * B * N * M / of / 1e6, 1)}))
 
 
+def cmd_icp():
+    """BASELINE config 3: the ICP block of train_ICP.py over 1200 synthetic pairs (2048 points,
+    threshold 0.02, <= 500 iterations, fixed initial rotation) in one launch; the CPU float64
+    restatement timed on a few pairs beside it."""
+    import time
+    from houv_b200 import icp, synth
+    from oracle import houv as oh
+    P = int(sys.argv[2]) if len(sys.argv) > 2 else 1200
+    s, t, tr = synth.make_pairs(0, P)
+    src, tgt, gt = (torch.from_numpy(a).cuda() for a in (s, t, tr))
+    med, best = timeit(lambda: icp.icp_batch(src, tgt, gt), iters=3, warmup=1)
+    reg = icp.registration_icp(src, tgt, icp.THRESHOLD, icp.TRANS_INIT, icp.MAX_ITERATION)
+    ans, r_err, t_err, mse = icp.icp_batch(src, tgt, gt)
+    n_cpu = 3
+    t0 = time.perf_counter()
+    for i in range(n_cpu):
+        oh.icp_point_to_point(s[i].astype(np.float64), t[i].astype(np.float64), 0.02,
+                              icp.TRANS_INIT.astype(np.float64), 500)
+    cpu = (time.perf_counter() - t0) / n_cpu
+    print(json.dumps({"kernel": "ICP (houv_icp)", "pairs": P, "ms": round(med, 2),
+                      "pairs_per_s": round(P / med * 1e3, 1),
+                      "iterations_mean": float(reg.iterations.mean()),
+                      "iterations_max": float(reg.iterations.max()),
+                      "fitness_mean": float(reg.fitness.mean()),
+                      "rot_err_deg_mean": float(r_err.mean()), "trans_err_mean": float(t_err.mean()),
+                      "cpu_oracle_s_per_pair": round(cpu, 3),
+                      "cpu_oracle_pairs_per_s": round(1.0 / cpu, 2)}))
+
+
 def cmd_pose():
     """K3 at the BASELINE shape: P pairs x 64 starts x `iters` iterations, 2048 points."""
     import numpy as np
@@ -163,4 +193,4 @@ def cmd_pose():
 
 
 if __name__ == "__main__":
-    {"probe": cmd_probe, "chamfer": cmd_chamfer, "pose": cmd_pose, "refext": cmd_refext}[sys.argv[1] if len(sys.argv) > 1 else "probe"]()
+    {"probe": cmd_probe, "chamfer": cmd_chamfer, "pose": cmd_pose, "refext": cmd_refext, "icp": cmd_icp}[sys.argv[1] if len(sys.argv) > 1 else "probe"]()
