@@ -79,3 +79,55 @@ def gather_results(ans, metrics, world):
     else:
         out = packed
     return out[:, :16].reshape(-1, 4, 4), out[:, 16:]
+
+
+# ----------------------------------------------------------------- result files
+# The reference's file-based merge, kept for drop-in use next to the all-gather:
+# every process saves its range as `{l}_{r}.npy` (test_mult.py:65-66) and a --combine pass
+# concatenates them into `results.h5`, dataset 'results' [P,4,4] float32 (test_mult.py:70-81;
+# test.py:67-77 writes the same file for a single process).
+
+def save_range(ans, log_dir, l, r):
+    """test_mult.py:65-66: np.save(log_dir + '/{l}_{r}.npy', all_results)."""
+    import numpy as np
+    os.makedirs(log_dir, exist_ok=True)
+    path = os.path.join(log_dir, '{}_{}.npy'.format(l, r))
+    np.save(path, ans.detach().cpu().numpy().astype('float32') if torch.is_tensor(ans) else ans)
+    return path
+
+
+def combine(log_dir, step=500, num=4):
+    """test_mult.py:70-81: concatenate the `num` range files of width `step` and write
+    results.h5 (dataset 'results').  h5py is an optional dependency: without it the merged
+    array is written as results.npy only.  A missing range file raises FileNotFoundError like
+    the reference's np.load.  -> the merged [P,4,4] array."""
+    import numpy as np
+    parts = [np.load(os.path.join(log_dir, '{}_{}.npy'.format(step * i, step * i + step)))
+             for i in range(num)]
+    all_results = np.concatenate(parts, axis=0)
+    np.save(os.path.join(log_dir, 'results.npy'), all_results)
+    try:
+        import h5py
+    except ImportError:
+        h5py = None
+    if h5py is not None:
+        with h5py.File(os.path.join(log_dir, 'results.h5'), 'w') as f:
+            f.create_dataset('results', data=all_results)
+    return all_results
+
+
+def load_mvp_pairs(path, l=None, r=None):
+    """The arrays MVP_RG_rotated(_bound) hands to the solver (dataset.py:189-233, 354-372):
+    'rotated_src' / 'rotated_tgt' [P,2048,3] float32 and, where the file has them (the val
+    split), 'transforms' [P,4,4].  Needs h5py (the MVP files are HDF5); -> (src, tgt, transforms
+    or None) as numpy arrays for the index range [l, r)."""
+    try:
+        import h5py
+    except ImportError as e:  # pragma: no cover
+        raise RuntimeError("reading MVP_*_RG.h5 needs h5py, which this environment lacks") from e
+    with h5py.File(path, 'r') as f:
+        sl = slice(l, r)
+        src = f['rotated_src'][sl].astype('float32')
+        tgt = f['rotated_tgt'][sl].astype('float32')
+        tr = f['transforms'][sl].astype('float32') if 'transforms' in f else None
+    return src, tgt, tr

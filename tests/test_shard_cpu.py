@@ -85,3 +85,20 @@ def test_gloo_world2_gather_matches_single_process():
     for rank, a, m in got:
         assert a.shape == (total, 4, 4) and m.shape == (total, 3)
         assert np.array_equal(a, ans.numpy()) and np.allclose(m, met.numpy())
+
+
+def test_range_files_and_combine(tmp_path):
+    """test_mult.py:65-81: per-range .npy files merged in index order; a missing range raises."""
+    import numpy as np
+    import pytest
+    import torch
+    from houv_b200 import shard
+    full = np.arange(8 * 16, dtype=np.float32).reshape(8, 4, 4)
+    for i in range(4):
+        p = shard.save_range(torch.from_numpy(full[2 * i:2 * i + 2]), str(tmp_path), 2 * i, 2 * i + 2)
+        assert p.endswith("%d_%d.npy" % (2 * i, 2 * i + 2))
+    merged = shard.combine(str(tmp_path), step=2, num=4)
+    assert merged.dtype == np.float32 and np.array_equal(merged, full)
+    assert np.array_equal(np.load(str(tmp_path / "results.npy")), full)
+    with pytest.raises(FileNotFoundError):
+        shard.combine(str(tmp_path), step=2, num=5)
