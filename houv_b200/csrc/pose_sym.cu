@@ -96,19 +96,29 @@ __device__ __forceinline__ void eval4(const float2 X, const float2 Y, const floa
 }
 
 // One rotation step: 8 rows x one column pair, kRG rows evaluated before their folds.
-template <int kRG>
+// kNM = 4: the four metrics of Predict_loss; kNM = 1: the 3-D metric alone (a loss without the
+// view terms, train_utils.py:439) -- 6 packed lane-ops and 2 min folds per evaluation.
+template <int kRG, int kNM>
 __device__ __forceinline__ void sym_step(const float2 X, const float2 Y, const float2 Z,
                                          const float (&nqx)[8], const float (&nqy)[8],
-                                         const float (&nqz)[8], float (&best)[4][8],
-                                         float (&cmx)[4], float (&cmy)[4]) {
+                                         const float (&nqz)[8], float (&best)[kNM][8],
+                                         float (&cmx)[kNM], float (&cmy)[kNM]) {
 #pragma unroll
     for (int r = 0; r < 8; r += kRG) {
         float2 v[kRG][4];
 #pragma unroll
-        for (int i = 0; i < kRG; ++i)
-            eval4(X, Y, Z, nqx[r + i], nqy[r + i], nqz[r + i], v[i][0], v[i][1], v[i][2], v[i][3]);
+        for (int i = 0; i < kRG; ++i) {
+            if (kNM == 4) {
+                eval4(X, Y, Z, nqx[r + i], nqy[r + i], nqz[r + i], v[i][0], v[i][1], v[i][2], v[i][3]);
+            } else {  // the same contraction as eval4's f: fma(dz,dz,fma(dx,dx,dy*dy))
+                const float2 dx = __fadd2_rn(X, make_float2(nqx[r + i], nqx[r + i]));
+                const float2 dy = __fadd2_rn(Y, make_float2(nqy[r + i], nqy[r + i]));
+                const float2 dz = __fadd2_rn(Z, make_float2(nqz[r + i], nqz[r + i]));
+                v[i][0] = __ffma2_rn(dz, dz, __ffma2_rn(dx, dx, __fmul2_rn(dy, dy)));
+            }
+        }
 #pragma unroll
-        for (int m = 0; m < 4; ++m) {
+        for (int m = 0; m < kNM; ++m) {
 #pragma unroll
             for (int i = 0; i < kRG; ++i) best[m][r + i] = min3(best[m][r + i], v[i][m].x, v[i][m].y);
 #pragma unroll
@@ -121,7 +131,7 @@ __device__ __forceinline__ void sym_step(const float2 X, const float2 Y, const f
 }
 
 // kSymUnroll: unroll of the 8 rotation steps of a phase
-template <int kSymUnroll, int kRG>
+template <int kSymUnroll, int kRG, int kNM>
 __global__ void __launch_bounds__(kSymThreads, 1) pose_sym_kernel(const PoseArgs A) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     SmemSym &S = *reinterpret_cast<SmemSym *>(smem_raw);
@@ -195,7 +205,7 @@ __global__ void __launch_bounds__(kSymThreads, 1) pose_sym_kernel(const PoseArgs
         }
         // row bookkeeping of this sweep: shadow = +inf, winning superblock = 0
 #pragma unroll
-        for (int k = 0; k < 32; ++k) S.shadow[k][t] = kInf;
+        for (int k = 0; k < 8 * kNM; ++k) S.shadow[k][t] = kInf;
         for (int i = t; i < 4 * 2 * kPts / 4; i += kSymThreads)
             reinterpret_cast<unsigned *>(&S.gid[0][0][0])[i] = 0u;
         for (int i = t; i < 4 * kPts / 4; i += kSymThreads)
@@ -203,7 +213,7 @@ __global__ void __launch_bounds__(kSymThreads, 1) pose_sym_kernel(const PoseArgs
         __syncthreads();
 
         // ---- (c) the symmetric sweep
-        float nqx[8], nqy[8], nqz[8], best[4][8];
+        float nqx[8], nqy[8], nqz[8], best[kNM][8];
         if (scan_active) {
 #pragma unroll
             for (int r = 0; r < 8; ++r) {
@@ -213,7 +223,7 @@ __global__ void __launch_bounds__(kSymThreads, 1) pose_sym_kernel(const PoseArgs
 #pragma unroll
         for (int r = 0; r < 8; ++r)
 #pragma unroll
-            for (int m = 0; m < 4; ++m) best[m][r] = kInf;
+            for (int m = 0; m < kNM; ++m) best[m][r] = kInf;
         float vcol = 0.f;  // sum sqrt(column minimum) of view metric rm (reducer role)
 
 #pragma unroll 1
@@ -224,9 +234,9 @@ __global__ void __launch_bounds__(kSymThreads, 1) pose_sym_kernel(const PoseArgs
 #pragma unroll 1
                 for (int ph = 0; ph < 4; ++ph) {
                     const int cb = (gq + ph) & 3;  // 16-column block of this group in this phase
-                    float cmx[4], cmy[4];  // running column minima of the pair in hand
+                    float cmx[kNM], cmy[kNM];  // running column minima of the pair in hand
 #pragma unroll
-                    for (int m = 0; m < 4; ++m) { cmx[m] = kInf; cmy[m] = kInf; }
+                    for (int m = 0; m < kNM; ++m) { cmx[m] = kInf; cmy[m] = kInf; }
                     const int cbase = sbbase + 16 * cb;
 #pragma unroll kSymUnroll
                     for (int s = 0; s < 8; ++s) {
@@ -234,10 +244,10 @@ __global__ void __launch_bounds__(kSymThreads, 1) pose_sym_kernel(const PoseArgs
                         const float2 X = *reinterpret_cast<const float2 *>(&S.tx[c]);
                         const float2 Y = *reinterpret_cast<const float2 *>(&S.ty[c]);
                         const float2 Z = *reinterpret_cast<const float2 *>(&S.tz[c]);
-                        sym_step<kRG>(X, Y, Z, nqx, nqy, nqz, best, cmx, cmy);
+                        sym_step<kRG, kNM>(X, Y, Z, nqx, nqy, nqz, best, cmx, cmy);
                         if (s < 7) {  // the column pair moves on to lane ll-1; ours comes from ll+1
 #pragma unroll
-                            for (int m = 0; m < 4; ++m) {
+                            for (int m = 0; m < kNM; ++m) {
                                 cmx[m] = __shfl_sync(0xffffffffu, cmx[m], ll + 1, 8);
                                 cmy[m] = __shfl_sync(0xffffffffu, cmy[m], ll + 1, 8);
                             }
@@ -246,12 +256,12 @@ __global__ void __launch_bounds__(kSymThreads, 1) pose_sym_kernel(const PoseArgs
                     // after step 7 this lane holds the finished pair (ll+7)&7 of block cb
                     const int pc = 16 * cb + 2 * ((ll + 7) & 7);
 #pragma unroll
-                    for (int m = 0; m < 4; ++m)
+                    for (int m = 0; m < kNM; ++m)
                         *reinterpret_cast<float2 *>(&S.part[half][sg][m][pc]) = make_float2(cmx[m], cmy[m]);
                 }
                 // rows: did this superblock strictly improve the running minimum?
 #pragma unroll
-                for (int m = 0; m < 4; ++m)
+                for (int m = 0; m < kNM; ++m)
 #pragma unroll
                     for (int r = 0; r < 8; ++r) {
                         const float prev = S.shadow[m * 8 + r][t];
@@ -264,7 +274,7 @@ __global__ void __launch_bounds__(kSymThreads, 1) pose_sym_kernel(const PoseArgs
             }
             __syncthreads();
             // columns: first sub-group (ascending rows) holding the minimum
-            {
+            if (rm < kNM) {
                 const int col = (rh * nsbh + rr) * kSB + rc;
                 float bv = kInf;
                 int bs = 0;
@@ -285,7 +295,7 @@ __global__ void __launch_bounds__(kSymThreads, 1) pose_sym_kernel(const PoseArgs
         for (int m = 0; m < 3; ++m) vs[0][m] = (rm == m + 1) ? vcol : 0.f;
         if (half == 0 && scan_active) {
 #pragma unroll
-            for (int m = 0; m < 4; ++m)
+            for (int m = 0; m < kNM; ++m)
 #pragma unroll
                 for (int r = 0; r < 8; ++r) {
                     const int i = row0 + r;
@@ -418,7 +428,7 @@ __global__ void __launch_bounds__(kSymThreads, 1) pose_sym_kernel(const PoseArgs
         for (int i = 0; i < 12; ++i) acc[i] = 0.f;
         const int lane = t & 31;
 #pragma unroll
-        for (int m = 0; m < 4; ++m) {
+        for (int m = 0; m < kNM; ++m) {
             if (m > 0 && A.wview == 0.f) continue;  // loss = w3d*min_1 only (train_utils.py:439)
             const int dir = side[m];
             // x, y, z of a cloud are consecutive kPts-float arrays: one base pointer per cloud
@@ -483,27 +493,29 @@ __global__ void __launch_bounds__(kSymThreads, 1) pose_sym_kernel(const PoseArgs
     if (t == 0) state_store(st, A, row);
 }
 
-template <int kU, int kRG>
+template <int kU, int kRG, int kNM>
 static int launch_sym(const PoseArgs &a, cudaStream_t st) {
     static bool attr_set = false;
     if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(pose_sym_kernel<kU, kRG>,
+        cudaError_t e = cudaFuncSetAttribute(pose_sym_kernel<kU, kRG, kNM>,
                                              cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              (int)sizeof(SmemSym));
         if (e != cudaSuccess) return (int)e;
         attr_set = true;
     }
-    pose_sym_kernel<kU, kRG><<<a.rows, kSymThreads, sizeof(SmemSym), st>>>(a);
+    pose_sym_kernel<kU, kRG, kNM><<<a.rows, kSymThreads, sizeof(SmemSym), st>>>(a);
     return check_launch();
 }
 
 int launch_pose_sym(const PoseArgs &a, int unroll, cudaStream_t st) {
+    // a loss without view terms (wview == 0: train_utils.getPredict_angle) needs the 3-D metric only
+    if (a.wview == 0.f && unroll != 1004) return launch_sym<8, 2, 1>(a, st);
     switch (unroll) {
-        case 4: return launch_sym<4, 2>(a, st);
-        case 8: return launch_sym<8, 2>(a, st);
-        case 84: return launch_sym<8, 4>(a, st);
-        case 44: return launch_sym<4, 4>(a, st);
-        default: return launch_sym<2, 2>(a, st);
+        case 4: return launch_sym<4, 2, 4>(a, st);
+        case 8: case 1004: return launch_sym<8, 2, 4>(a, st);
+        case 84: return launch_sym<8, 4, 4>(a, st);
+        case 44: return launch_sym<4, 4, 4>(a, st);
+        default: return launch_sym<2, 2, 4>(a, st);
     }
 }
 

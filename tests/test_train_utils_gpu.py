@@ -108,3 +108,22 @@ def test_float64_state_trajectory_vs_oracle():
     # first-step gradients from the float64 first moment: m_1 = (1-beta1) g
     g_gpu = (m.cpu().numpy() / (1 - 0.9 ** 20))  # only its sign/size is sanity-checked below
     assert np.isfinite(g_gpu).all() and params.dtype == torch.float64
+
+
+def test_one_metric_sweep_equals_four_metric_sweep():
+    """wview == 0 selects the 3-D-only specialisation of the symmetric sweep; variant 15 forces the
+    four-metric sweep on the same problem: identical bits (the view terms never reach the loss)."""
+    from houv_b200 import _lib, solver, train_utils as tu
+    s, t, _ = synth.make_pairs(21, 2, n_points=320)
+    src, tgt = torch.from_numpy(s).cuda(), torch.from_numpy(t).cuda()
+    outs = []
+    for variant in (12, 15):
+        _lib.load().houv_set_pose_variant(variant)
+        np.random.seed(9)
+        params = torch.from_numpy(tu.initial_variables(32)).cuda()
+        o = solver.pose_optimise(src, tgt, params, 16, 12, lr=0.1, wview=0.0, tran_scale=1.0,
+                                 tran_offset=0.0, want_trace=True, want_tran_s=True)
+        outs.append((params.clone(), o))
+    (p0, o0), (p1, o1) = outs
+    assert torch.equal(p0, p1) and torch.equal(o0["trace"], o1["trace"])
+    assert torch.equal(o0["R"], o1["R"]) and torch.equal(o0["tran_s"], o1["tran_s"])

@@ -127,6 +127,29 @@ def cmd_refext():
                           "ours_Gpts2_per_s": round(2.0 * B * N * M / of / 1e6, 1)}))
 
 
+def cmd_solve():
+    """train_utils.getPredict_angle shape: P pairs x 64 starts x `iters` iterations
+    at lr 0.1 with the 3-D term only; one-metric sweep (default) vs the four-metric sweep."""
+    from houv_b200 import solver, synth, train_utils as tu
+    P = int(sys.argv[2]) if len(sys.argv) > 2 else 37
+    iters = int(sys.argv[3]) if len(sys.argv) > 3 else 40
+    s, t, _ = synth.make_pairs(0, P)
+    src, tgt = torch.from_numpy(s).cuda(), torch.from_numpy(t).cuda()
+    np.random.seed(0)
+    init = torch.from_numpy(tu.initial_variables(P * 64)).cuda()
+
+    def run():
+        solver.pose_optimise(src, tgt, init.clone(), 64, iters, lr=0.1, wview=0.0, tran_scale=1.0,
+                             tran_offset=0.0)
+    for v in (12, 15):
+        _lib.load().houv_set_pose_variant(v)
+        med, best = timeit(run, iters=3, warmup=1)
+        print(json.dumps({"variant": v, "ms": round(med, 2),
+                          "us_per_row_iter_per_sm": round(med * 1e3 / (P * 64 * iters) * 148, 1),
+                          "pairs_per_s_500its": round(P / (med * 500 / iters) * 1e3, 2)}))
+    _lib.load().houv_set_pose_variant(-1)
+
+
 def cmd_icp():
     """BASELINE config 3: the ICP block of train_ICP.py over 1200 synthetic pairs (2048 points,
     threshold 0.02, <= 500 iterations, fixed initial rotation) in one launch; the CPU float64
@@ -193,4 +216,4 @@ def cmd_pose():
 
 
 if __name__ == "__main__":
-    {"probe": cmd_probe, "chamfer": cmd_chamfer, "pose": cmd_pose, "refext": cmd_refext, "icp": cmd_icp}[sys.argv[1] if len(sys.argv) > 1 else "probe"]()
+    {"probe": cmd_probe, "chamfer": cmd_chamfer, "pose": cmd_pose, "refext": cmd_refext, "icp": cmd_icp, "solve": cmd_solve}[sys.argv[1] if len(sys.argv) > 1 else "probe"]()
