@@ -211,6 +211,11 @@ def run_ours(args):
 
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device: houv_b200 has no CPU path")
+    # stdout must carry exactly ONE JSON line, but NCCL printf()s its version banner there when the
+    # communicator comes up: point fd 1 at stderr until the line is ready
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
     rank, world, local = shard.init_distributed()
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
@@ -368,7 +373,10 @@ def run_ours(args):
             "sample": "1 pair x %d starts x %d of %d Adam iterations at angle_base 0 in %.1f s "
                       "(CPU oracle: restated houv.py over the C chamfer oracle on %d threads), "
                       "linearly extrapolated, retries not added" % (KERNEL, n_it, ITERS, sec, cores)}
+    sys.stdout.flush()
+    os.dup2(real_stdout, 1)
     print(json.dumps(line))
+    sys.stdout.flush()
 
 
 if __name__ == "__main__":

@@ -172,8 +172,17 @@ static int dispatch_nn(const NNArgs &a, int ndir, cudaStream_t st) {
         case 1: return launch_nn<4, 128>(a, ndir, st);
         case 2: return launch_nn<4, 64>(a, ndir, st);
         case 3: return launch_nn<2, 256>(a, ndir, st);
-        case 0:
-        default: return launch_nn<2, 128>(a, ndir, st);
+        case 4: return launch_nn<2, 64>(a, ndir, st);
+        case 5: return launch_nn<1, 128>(a, ndir, st);
+        case 6: return launch_nn<1, 64>(a, ndir, st);
+        case 0: return launch_nn<2, 128>(a, ndir, st);
+        default: {
+            // automatic: one query per thread gives twice the CTAs (better balance over 148 SMs,
+            // measured 5-25 % faster up to C5 size); two per thread once the grid is many waves deep
+            const long long queries = (long long)a.B * (a.dir[0].n + (ndir == 2 ? a.dir[1].n : 0));
+            return queries > 4000000LL ? launch_nn<2, 128>(a, ndir, st)
+                                       : launch_nn<1, 128>(a, ndir, st);
+        }
     }
 }
 

@@ -68,7 +68,7 @@ def cmd_chamfer():
         d2 = torch.empty(B, M, device="cuda")
         i1 = torch.empty(B, N, device="cuda", dtype=torch.int32)
         i2 = torch.empty(B, M, device="cuda", dtype=torch.int32)
-        for variant in (0, 1, 10):
+        for variant in [int(v) for v in os.environ.get('NN_VARIANTS', '0,1,10').split(',')]:
             lib.houv_set_nn_variant(variant)
             med, best = timeit(lambda: chamfer_3D.forward(x1, x2, d1, d2, i1, i2), flush=flush)
             evals = 2.0 * B * N * M
