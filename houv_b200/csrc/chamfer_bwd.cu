@@ -11,6 +11,8 @@
 // then float atomics (RED.ADD.F32.FTZ.RN) into both gradient buffers, which the
 // caller zero-fills.  Like the reference the summation ORDER of colliding
 // scatters is not deterministic.
+#include <stdlib.h>
+
 #include "common.cuh"
 
 namespace houv {
@@ -28,7 +30,24 @@ struct GradArgs {
     GradDir dir[2];
     long long split;  // elements of direction 0 (= B*N)
     long long total;  // B*(N+M)
+    bool vec;         // both gradient buffers are 4-byte aligned at least (always) and the
+                      // vector form is allowed (HOUV_K2_SCALAR unset)
 };
+
+// Three float atomics on an xyz triple as one 8-byte vector RED (red.global.add.v2.f32, sm_90+)
+// plus one scalar RED: the triple starts 8-byte aligned for even points (x,y | z) and 4 mod 8 for
+// odd ones (x | y,z).  Element-wise the additions are the same float atomics as before.
+__device__ __forceinline__ void red3(float *o, float a, float b, float c, bool vec) {
+    if (!vec) {
+        atomicAdd(o, a); atomicAdd(o + 1, b); atomicAdd(o + 2, c);
+    } else if ((reinterpret_cast<uintptr_t>(o) & 7) == 0) {
+        atomicAdd(reinterpret_cast<float2 *>(o), make_float2(a, b));
+        atomicAdd(o + 2, c);
+    } else {
+        atomicAdd(o, a);
+        atomicAdd(reinterpret_cast<float2 *>(o + 1), make_float2(b, c));
+    }
+}
 
 __global__ void __launch_bounds__(256) grad_kernel(const GradArgs args) {
     for (long long e = blockIdx.x * 256LL + threadIdx.x; e < args.total;
@@ -51,12 +70,11 @@ __global__ void __launch_bounds__(256) grad_kernel(const GradArgs args) {
         const float g = __fmul_rn(D.gd[w], 2.f);
         float *oa = D.ga + w * 3;
         float *ob = D.gb + (bi * D.m + j2) * 3;
+        float v[3];
 #pragma unroll
-        for (int k = 0; k < 3; ++k) {
-            float v = __fmul_rn(g, __fsub_rn(__ldg(pa + k), __ldg(pb + k)));
-            atomicAdd(oa + k, v);
-            atomicAdd(ob + k, -v);
-        }
+        for (int k = 0; k < 3; ++k) v[k] = __fmul_rn(g, __fsub_rn(__ldg(pa + k), __ldg(pb + k)));
+        red3(oa, v[0], v[1], v[2], args.vec);
+        red3(ob, -v[0], -v[1], -v[2], args.vec);
     }
 }
 
@@ -77,6 +95,8 @@ extern "C" int houv_chamfer3d_backward(const float *xyz1, const float *xyz2,
     a.dir[1] = GradDir{xyz2, xyz1, graddist2, idx2, gradxyz2, gradxyz1, M, N};
     a.split = (long long)B * N;
     a.total = (long long)B * ((long long)N + M);
+    static const bool scalar_only = getenv("HOUV_K2_SCALAR") != nullptr;
+    a.vec = !scalar_only;
     long long blocks = (a.total + 255) / 256;
     const long long cap = 148LL * 8 * 4;  // grid-stride beyond a few waves
     if (blocks > cap) blocks = cap;
