@@ -47,7 +47,10 @@ struct SmemSym {
     unsigned char gid[4][2][kPts];        // winning group: [m][0][col] = 64-row sub-group, [m][1][row] = superblock
     unsigned char rgid1[4][kPts];         // rows: winning superblock seen by the upper column half
     float part[2][32][4][kSB];            // [column half][sub-group][metric][column]: partial column minima
-    float shadow[32][kSymThreads];        // row minima as of the last superblock boundary, [metric*8+r][thread]
+    // row minima as of the last superblock boundary: per thread 8 float4 chunks, chunk c = values
+    // k = 4c..4c+3 (k = metric*8 + r), stored at position c ^ (thread & 7) so that the LDS.128 /
+    // STS.128 of 8 neighbouring threads hit 8 different bank groups
+    float4 shadow[kSymThreads][8];
     int hist[2][256];
     float red[kSymThreads / 32][16];
     float pose[12];
@@ -205,7 +208,7 @@ __global__ void __launch_bounds__(kSymThreads, 1) pose_sym_kernel(const PoseArgs
         }
         // row bookkeeping of this sweep: shadow = +inf, winning superblock = 0
 #pragma unroll
-        for (int k = 0; k < 8 * kNM; ++k) S.shadow[k][t] = kInf;
+        for (int c = 0; c < 2 * kNM; ++c) S.shadow[t][c ^ (t & 7)] = make_float4(kInf, kInf, kInf, kInf);
         for (int i = t; i < 4 * 2 * kPts / 4; i += kSymThreads)
             reinterpret_cast<unsigned *>(&S.gid[0][0][0])[i] = 0u;
         for (int i = t; i < 4 * kPts / 4; i += kSymThreads)
@@ -259,18 +262,26 @@ __global__ void __launch_bounds__(kSymThreads, 1) pose_sym_kernel(const PoseArgs
                     for (int m = 0; m < kNM; ++m)
                         *reinterpret_cast<float2 *>(&S.part[half][sg][m][pc]) = make_float2(cmx[m], cmy[m]);
                 }
-                // rows: did this superblock strictly improve the running minimum?
+                // rows: did this superblock strictly improve the running minimum?  One bit per
+                // (metric, row); the shadow is refreshed unconditionally (best <= shadow always)
+                unsigned improved = 0;
 #pragma unroll
-                for (int m = 0; m < kNM; ++m)
-#pragma unroll
-                    for (int r = 0; r < 8; ++r) {
-                        const float prev = S.shadow[m * 8 + r][t];
-                        if (best[m][r] < prev) {
-                            S.shadow[m * 8 + r][t] = best[m][r];
-                            if (half) S.rgid1[m][row0 + r] = (unsigned char)sb;
-                            else S.gid[m][1][row0 + r] = (unsigned char)sb;
-                        }
-                    }
+                for (int c = 0; c < 2 * kNM; ++c) {
+                    const int m = c >> 1, r0 = 4 * (c & 1);
+                    float4 &slot = S.shadow[t][c ^ (t & 7)];
+                    const float4 pv = slot;
+                    improved |= (best[m][r0 + 0] < pv.x ? 1u : 0u) << (4 * c + 0);
+                    improved |= (best[m][r0 + 1] < pv.y ? 1u : 0u) << (4 * c + 1);
+                    improved |= (best[m][r0 + 2] < pv.z ? 1u : 0u) << (4 * c + 2);
+                    improved |= (best[m][r0 + 3] < pv.w ? 1u : 0u) << (4 * c + 3);
+                    slot = make_float4(best[m][r0], best[m][r0 + 1], best[m][r0 + 2], best[m][r0 + 3]);
+                }
+                while (improved) {  // rarer and rarer as the sweep proceeds
+                    const int k = __ffs(improved) - 1;
+                    improved &= improved - 1;
+                    if (half) S.rgid1[k >> 3][row0 + (k & 7)] = (unsigned char)sb;
+                    else S.gid[k >> 3][1][row0 + (k & 7)] = (unsigned char)sb;
+                }
             }
             __syncthreads();
             // columns: first sub-group (ascending rows) holding the minimum
@@ -300,7 +311,8 @@ __global__ void __launch_bounds__(kSymThreads, 1) pose_sym_kernel(const PoseArgs
                 for (int r = 0; r < 8; ++r) {
                     const int i = row0 + r;
                     float b = best[m][r];
-                    const float b1 = S.shadow[m * 8 + r][t + 256];
+                    const float4 o4 = S.shadow[t + 256][(2 * m + (r >> 2)) ^ (t & 7)];  // (t+256)&7 == t&7
+                    const float b1 = (r & 3) == 0 ? o4.x : (r & 3) == 1 ? o4.y : (r & 3) == 2 ? o4.z : o4.w;
                     if (b1 < b) {
                         b = b1;
                         S.gid[m][1][i] = S.rgid1[m][i];
