@@ -150,6 +150,83 @@ def cmd_solve():
     _lib.load().houv_set_pose_variant(-1)
 
 
+def cmd_refhouv():
+    """The reference's HOUV loop as the reference runs it on a GPU, for a GPU-side baseline of
+    pairs/s: restated predict_model loop (houv.py:106-138: torch HOUV.forward, Predict_loss =
+    4 chamfer calls + 8 top-k sorts, autograd backward, torch Adam) over the reference's OWN CUDA
+    extension (oracle/_ref/chamfer_3D.so) with the reference wrapper's allocation pattern (CPU
+    zeros copied to the device per call, dist_chamfer_3D.py:33-42,56-60).  B pairs x 64 starts,
+    `n` timed iterations; pairs/s = B / (t_iter * 200), retries not added."""
+    from torch.autograd import Function
+    from houv_b200 import loss as L, solver, synth
+    from oracle import ref_ext
+    ref = ref_ext.load()
+    faithful = os.environ.get("REF_ALLOC", "cpu") == "cpu"
+
+    def zeros(shape, dev, dtype=torch.float32):
+        if faithful:
+            z = torch.zeros(*shape)
+            return (z.type(torch.IntTensor) if dtype == torch.int32 else z).to(dev)
+        return torch.zeros(*shape, device=dev, dtype=dtype)
+
+    class RefFn(Function):  # dist_chamfer_3D.py:26-64
+        @staticmethod
+        def forward(ctx, xyz1, xyz2):
+            B, n, _ = xyz1.shape
+            m = xyz2.shape[1]
+            dev = xyz1.device
+            d1, d2 = zeros((B, n), dev), zeros((B, m), dev)
+            i1, i2 = zeros((B, n), dev, torch.int32), zeros((B, m), dev, torch.int32)
+            ref.forward(xyz1, xyz2, d1, d2, i1, i2)
+            ctx.save_for_backward(xyz1, xyz2, i1, i2)
+            return d1, d2, i1, i2
+
+        @staticmethod
+        def backward(ctx, g1, g2, gi1, gi2):
+            xyz1, xyz2, i1, i2 = ctx.saved_tensors
+            gx1, gx2 = zeros(tuple(xyz1.shape), xyz1.device), zeros(tuple(xyz2.shape), xyz2.device)
+            ref.backward(xyz1, xyz2, gx1, gx2, g1.contiguous(), g2.contiguous(), i1, i2)
+            return gx1, gx2
+
+    class RefCd(torch.nn.Module):
+        def forward(self, a, b):
+            return RefFn.apply(a.contiguous(), b.contiguous())
+
+    B = int(sys.argv[2]) if len(sys.argv) > 2 else 8
+    n_it = int(sys.argv[3]) if len(sys.argv) > 3 else 5
+    s, t, _ = synth.make_pairs(0, B)
+    src = torch.from_numpy(s).cuda().unsqueeze(1).expand(-1, 64, -1, -1).reshape(-1, 2048, 3)
+    tgt = torch.from_numpy(t).cuda().unsqueeze(1).expand(-1, 64, -1, -1).reshape(-1, 2048, 3)
+    old_cd = L.cd
+    L.cd = RefCd
+    try:
+        net = solver.HOUV(B * 64, 0)
+        net.reset_weight(B * 64, 0)
+        opt = torch.optim.Adam(net.parameters(), lr=0.01)
+
+        def it():
+            opt.zero_grad()
+            src_temp, R, T = net(src)
+            rmse, min_1 = L.Predict_loss(src_temp, tgt)
+            rmse.mean().backward()
+            opt.step()
+        it(); it()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(n_it):
+            it()
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / n_it
+    finally:
+        L.cd = old_cd
+    print(json.dumps({"what": "reference HOUV loop on the reference CUDA ext", "pairs": B,
+                      "alloc": "cpu zeros + H2D (reference wrapper)" if faithful else "device zeros",
+                      "ms_per_iteration": round(ms, 2),
+                      "pairs_per_s_200its": round(B / (ms * 200 / 1e3), 4)}))
+
+
 def cmd_icp():
     """BASELINE config 3: the ICP block of train_ICP.py over 1200 synthetic pairs (2048 points,
     threshold 0.02, <= 500 iterations, fixed initial rotation) in one launch; the CPU float64
@@ -216,4 +293,4 @@ def cmd_pose():
 
 
 if __name__ == "__main__":
-    {"probe": cmd_probe, "chamfer": cmd_chamfer, "pose": cmd_pose, "refext": cmd_refext, "icp": cmd_icp, "solve": cmd_solve}[sys.argv[1] if len(sys.argv) > 1 else "probe"]()
+    {"probe": cmd_probe, "chamfer": cmd_chamfer, "pose": cmd_pose, "refext": cmd_refext, "icp": cmd_icp, "solve": cmd_solve, "refhouv": cmd_refhouv}[sys.argv[1] if len(sys.argv) > 1 else "probe"]()
