@@ -29,7 +29,8 @@ class HouvPoseProblem(ctypes.Structure):
                 ("min1_out", _fp), ("loss_out", _fp), ("R_out", _fp), ("T_out", _fp),
                 ("tran_s_out", _fp), ("trace", _fp),
                 ("row_pair", _fp), ("row_base", _fp),
-                ("rows", _ci)]
+                ("rows", _ci),
+                ("row_scale", _fp)]
 
 
 # name -> argtypes; every entry point returns int (0 = ok) unless noted

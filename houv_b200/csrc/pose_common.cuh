@@ -34,6 +34,7 @@ struct PoseArgs {
     // feeds their float32 roundings to the forward, train_utils.py:382-401); null = float32 state
     double *params64, *adam_m64, *adam_v64;
     float *tran_s_out;  // [rows] |T| of the last forward, or null
+    const float *row_scale;  // [rows] per-row grad_scale, or null (= grad_scale)
 };
 
 // squared distance of metric m between (tx,ty,tz) and (qx,qy,qz), scalar, same

@@ -180,6 +180,8 @@ __global__ void __launch_bounds__(kThreads, 2) pose_kernel(const PoseArgs A) {
     const int abase = A.row_base ? A.row_base[row] : A.angle_base;
     const float boff = (float)((double)abase * 3.14159274101257324 / 4.0);
     const int k3d = A.k3d;
+    // d(mean over the batch)/d(row): per row when rows of several batches share the launch
+    const float gscale = A.row_scale ? A.row_scale[row] : A.grad_scale;
 
     for (int it = 0; it < A.iters; ++it) {
         // ---- (a) pose from the 8 scalars
@@ -358,7 +360,7 @@ __global__ void __launch_bounds__(kThreads, 2) pose_kernel(const PoseArgs A) {
             const float *tX = dir ? S.tx : S.yx, *tY = dir ? S.ty : S.yy, *tZ = dir ? S.tz : S.yz;
             const int nq = dir ? N : M;
             // d(mean over rows)/d(row) * weight / k      houv.py:124,222; m_u_c.py:94-95
-            const float coef = A.grad_scale * (m == 0 ? A.w3d : A.wview) / (float)(m == 0 ? k3d : N);
+            const float coef = gscale * (m == 0 ? A.w3d : A.wview) / (float)(m == 0 ? k3d : N);
             for (int q = t; q < nq; q += kThreads) {
                 float wt = 1.f;
                 if (m == 0) {  // top-k membership of the trimmed 3-D term
@@ -457,6 +459,7 @@ extern "C" int houv_pose_optimise_ex(const HouvPoseProblem *q, void *stream) {
     a.params64 = q->params64; a.adam_m64 = q->adam_m64; a.adam_v64 = q->adam_v64;
     a.min1_out = q->min1_out; a.loss_out = q->loss_out; a.R_out = q->R_out; a.T_out = q->T_out;
     a.tran_s_out = q->tran_s_out; a.trace = q->trace; a.row_pair = q->row_pair; a.row_base = q->row_base;
+    a.row_scale = q->row_scale;
     a.P = q->P; a.N = q->N; a.M = q->M; a.K = q->K; a.rows = rows;
     a.step0 = q->step0; a.iters = q->iters; a.angle_base = q->angle_base;
     a.k3d = (int)((double)q->N * (double)q->percent);

@@ -179,6 +179,8 @@ __global__ void __launch_bounds__(kSymThreads, 1) pose_sym_kernel(const PoseArgs
     const int abase = A.row_base ? A.row_base[row] : A.angle_base;
     const float boff = (float)((double)abase * 3.14159274101257324 / 4.0);
     const int k3d = A.k3d;
+    // d(mean over the batch)/d(row): per row when rows of several batches share the launch
+    const float gscale = A.row_scale ? A.row_scale[row] : A.grad_scale;
 
     // role of this thread in the per-superblock column reduction: metric rm, column rc of the
     // 128 columns (64 per half) finished in a round
@@ -447,7 +449,7 @@ __global__ void __launch_bounds__(kSymThreads, 1) pose_sym_kernel(const PoseArgs
             const float *qB = dir ? S.yx : S.tx, *tB = dir ? S.tx : S.yx;
             const int nq = dir ? N : M;
             // d(mean over rows)/d(row) * weight / k      houv.py:124,222; m_u_c.py:94-95
-            const float coef = A.grad_scale * (m == 0 ? A.w3d : A.wview) / (float)(m == 0 ? k3d : N);
+            const float coef = gscale * (m == 0 ? A.w3d : A.wview) / (float)(m == 0 ? k3d : N);
             for (int q = t; q < nq; q += kSymThreads) {
                 float wt = 1.f;
                 if (m == 0) {  // top-k membership of the trimmed 3-D term

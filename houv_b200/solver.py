@@ -121,13 +121,14 @@ def pose_optimise(src, tgt, params, kernel, iters, angle_base=0, grad_scale=None
                   adam_m=None, adam_v=None, step0=0, lr=ADAM_LR, betas=ADAM_BETAS, eps=ADAM_EPS,
                   percent=ALPHA, w3d=W_3D, wview=W_VIEW, want_loss=False, want_trace=False,
                   row_pair=None, row_base=None, tran_scale=0.125, tran_offset=0.125,
-                  want_tran_s=False):
+                  want_tran_s=False, row_scale=None):
     """Thin wrapper over the C ABI houv_pose_optimise_ex (K3).
     src[P,N,3], tgt[P,N,3] device float32; params[P*kernel,8] is updated IN PLACE: float32
     (HOUV, houv.py) or float64 (train_utils.getPredict_angle keeps float64 leaves; adam_m /
     adam_v must then be float64 too).
     row_pair / row_base (int32 device tensors [rows]) optionally map every row to a pair
     and an angle_base of its own; rows is then params.shape[0] instead of P*kernel.
+    row_scale (float32 [rows]) gives every row its own grad_scale (several batches in one launch).
     -> dict(min_1[rows], R[rows,3,3], T[rows,3], loss[rows]|None, trace[iters,rows,2]|None,
             tran_s[rows]|None)"""
     _lib.require_cuda_f32(src, "src", 3)
@@ -175,7 +176,11 @@ def pose_optimise(src, tgt, params, kernel, iters, angle_base=0, grad_scale=None
     q.tran_scale, q.tran_offset = tran_scale, tran_offset
     q.min1_out, q.loss_out, q.R_out, q.T_out = min1.data_ptr(), ptr(loss), R.data_ptr(), T.data_ptr()
     q.tran_s_out, q.trace = ptr(tran_s), ptr(trace)
+    if row_scale is not None and (row_scale.dtype != torch.float32 or not row_scale.is_cuda
+                                  or row_scale.numel() != rows or not row_scale.is_contiguous()):
+        raise RuntimeError("row_scale must be a contiguous float32 CUDA tensor of [rows]")
     q.row_pair, q.row_base, q.rows = ptr(row_pair), ptr(row_base), rows
+    q.row_scale = ptr(row_scale)
     timing = KERNEL_TIMING
     if timing is not None:
         ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -262,3 +267,73 @@ def solve_model(net, src, src_rotated, pose=None, src_ori=None, tgt_ori=None, an
     t_err = translation_error(ans[:, :3, 3], pose[:, :3, 3])
     print("Rotation error:", r_err.mean(), "Translation error:", t_err.mean())
     return r_err, t_err, ans
+
+
+def solve_model_batches(src, src_rotated, batch_size=50, kernel=64, num_epochs=200):
+    """solve_model (houv.py:142-206) for a whole set of pairs walked in batches of `batch_size`
+    as train_HOUV.py:100-112 does, with the SAME per-pair results as calling solve_model batch by
+    batch -- initial values by position in the batch (houv.py:116), gradient scale 1/(rows of
+    the batch) (:124), retries at angle_base 1..3 on each batch's own sub-batch (:154-180) -- but
+    in TWO launches for the whole set (all first passes, then all retries) instead of two per
+    batch, which removes the partial last wave of every batch.  -> ans[P,4,4] on the device."""
+    src, src_rotated = src.float().contiguous(), src_rotated.float().contiguous()
+    P, dev = src.shape[0], src.device
+    if P == 0:
+        return torch.zeros(0, 4, 4, device=dev)
+    bounds = [(l, min(l + batch_size, P)) for l in range(0, P, batch_size)]
+    # row i of reset_weight's draws does not depend on the number of rows (initial_parameters)
+    init = torch.from_numpy(initial_parameters(min(batch_size, P) * kernel)).to(dev)
+    params = torch.cat([init[:(r - l) * kernel] for l, r in bounds]).contiguous()
+    scale = torch.cat([torch.full(((r - l) * kernel,), 1.0 / ((r - l) * kernel), device=dev)
+                       for l, r in bounds]).contiguous()
+    out = pose_optimise(src, src_rotated, params, kernel, num_epochs, angle_base=0, row_scale=scale)
+    rmse_loss = out["min_1"].reshape(P, kernel)
+    R = out["R"].reshape(P, kernel, 3, 3)
+    T = out["T"].reshape(P, kernel, 3)
+    rmse = rmse_loss.min(dim=1).values
+    lst_add = torch.nonzero(rmse > RETRY_THRESHOLD).reshape(-1)  # ascending = batch order
+    n_add = int(lst_add.numel())
+    if n_add > 0:
+        batch_of = (lst_add // batch_size).cpu()
+        counts = torch.bincount(batch_of, minlength=len(bounds)).tolist()
+        p_rows, pair_rows, base_rows, scale_rows, first = [], [], [], [], 0
+        for nb in counts:  # rows laid out [batch][angle_base][pair][start]
+            if nb == 0:
+                continue
+            sub_rows = nb * kernel
+            local = torch.arange(first, first + nb, device=dev, dtype=torch.int32) \
+                .repeat_interleave(kernel)
+            for b in (1, 2, 3):
+                p_rows.append(init[:sub_rows])
+                pair_rows.append(local)
+                base_rows.append(torch.full((sub_rows,), b, device=dev, dtype=torch.int32))
+                scale_rows.append(torch.full((sub_rows,), 1.0 / sub_rows, device=dev))
+            first += nb
+        out2 = pose_optimise(src[lst_add], src_rotated[lst_add], torch.cat(p_rows).contiguous(),
+                             kernel, num_epochs, row_pair=torch.cat(pair_rows).contiguous(),
+                             row_base=torch.cat(base_rows).contiguous(),
+                             row_scale=torch.cat(scale_rows).contiguous())
+        # back to [angle_base][pair] order, then the reference's keep-if-better sequence
+        order, off, first = [[], [], []], 0, 0
+        for nb in counts:
+            for b in range(3):
+                order[b].append(torch.arange(off, off + nb * kernel, device=dev))
+                off += nb * kernel
+        for b in range(3):
+            sel = torch.cat(order[b])
+            l_add = out2["min_1"][sel].reshape(n_add, kernel)
+            R_add = out2["R"][sel].reshape(n_add, kernel, 3, 3)
+            T_add = out2["T"][sel].reshape(n_add, kernel, 3)
+            rmse_add = l_add.min(dim=1).values
+            flag = torch.nonzero(rmse_add < rmse[lst_add]).reshape(-1)
+            geid = lst_add[flag]
+            R[geid] = R_add[flag]
+            rmse_loss[geid] = l_add[flag]
+            T[geid] = T_add[flag]
+            rmse[geid] = rmse_add[flag]
+    best = rmse_loss.argmin(dim=1)
+    rows = torch.arange(P, device=dev)
+    ans = torch.zeros((P, 4, 4), device=dev)
+    ans[:, :3, :3] = R[rows, best]
+    ans[:, :3, 3] = T[rows, best]
+    return ans

@@ -121,6 +121,8 @@ typedef struct HouvPoseProblem {
     float *min1_out, *loss_out, *R_out, *T_out, *tran_s_out, *trace;
     const int *row_pair, *row_base;
     int rows;                        /* 0 = P*K */
+    const float *row_scale;          /* [rows] per-row grad_scale (rows of several batches in one
+                                        launch, each batch with its own 1/rows_in_batch), or NULL */
 } HouvPoseProblem;
 int houv_pose_optimise_ex(const HouvPoseProblem *problem, void *stream);
 

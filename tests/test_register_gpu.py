@@ -182,3 +182,39 @@ def test_icp_batch_metrics_shape():
                                        torch.from_numpy(tr).cuda())
     assert ans.shape == (5, 4, 4) and r_err.shape == (5,) and t_err.shape == (5,) and mse.shape == (5,)
     assert torch.isfinite(ans).all()
+
+
+@pytest.mark.parametrize("variant", [12, 0])
+def test_merged_batches_equal_batch_by_batch(variant):
+    """shard.register_pairs launches every batch's first pass together and every batch's retries
+    together (solver.solve_model_batches, per-row gradient scale): bit-identical poses to calling
+    solve_model batch by batch as train_HOUV.py does, including a ragged last batch and retries."""
+    from houv_b200 import _lib, shard, solver
+    _lib.load().houv_set_pose_variant(variant)
+    try:
+        s, t, tr = synth.make_pairs(40, 7, n_points=192)
+        src, tgt = torch.from_numpy(s).cuda(), torch.from_numpy(t).cuda()
+        best = []
+        for l in range(0, 7, 3):  # first-pass best of every pair -> a threshold that splits them
+            r = min(l + 3, 7)
+            l0, _, _ = solver.predict_model(solver.HOUV((r - l) * 32, 0), src[l:r], tgt[l:r],
+                                            kernel=32, num_epochs=10)
+            best.append(l0.min(dim=1).values)
+        best = torch.cat(best)
+        old = solver.RETRY_THRESHOLD
+        solver.RETRY_THRESHOLD = float(best.median())  # 3 of 7 pairs retried, in several batches
+        retried = int((best > solver.RETRY_THRESHOLD).sum())
+        try:
+            ans, _ = shard.register_pairs(src, tgt, None, batch_size=3, kernel=32, num_epochs=10)
+            ref = []
+            for l in range(0, 7, 3):
+                r = min(l + 3, 7)
+                net = solver.HOUV((r - l) * 32, 0)
+                ref.append(solver.solve_model(net, src[l:r], tgt[l:r], None, kernel=32,
+                                              num_epochs=10, prefix='device'))
+        finally:
+            solver.RETRY_THRESHOLD = old
+        assert torch.equal(ans, torch.cat(ref))
+        assert 0 < retried  # the fixture does exercise the retry launch
+    finally:
+        _lib.load().houv_set_pose_variant(-1)
