@@ -21,7 +21,7 @@
 namespace houv {
 
 constexpr int kIcpPts = 2048;
-constexpr int kIcpThreads = 256;
+constexpr int kIcpThreads = 512;
 constexpr int kIcpQ = 4;
 constexpr int kIcpG = 8;
 constexpr int kIcpSums = 17;  // count, sum d^2, sum y[3], sum t[3], sum y t^T [9]
