@@ -22,6 +22,25 @@ RETRY_THRESHOLD = 0.030  # train_utils.py:493
 SOLVE_EPOCHS = 500       # train_utils.py:488,503 pass the literal 500, not solve's argument
 
 
+class AverageValueMeter(object):
+    """train_utils.py:22-36: running mean used by every entry script's logging."""
+
+    def __init__(self):
+        self.reset()
+
+    def reset(self):
+        self.val = 0
+        self.avg = 0
+        self.sum = 0
+        self.count = 0.0
+
+    def update(self, val, n=1):
+        self.val = val
+        self.sum += val * n
+        self.count += n
+        self.avg = self.sum / self.count
+
+
 def rotation(angle, V, device='cuda'):
     """train_utils.py:113-130: Rodrigues rotation from angle[B,1] and axis V[B,3]."""
     batch_size = angle.shape[0]
