@@ -38,6 +38,7 @@ _SIGNATURES = {
     "houv_chamfer3d_forward": [_vp, _vp, _ci, _ci, _ci, _vp, _vp, _vp, _vp, _vp],
     "houv_chamfer3d_forward_ws": [_vp, _vp, _ci, _ci, _ci, _vp, _vp, _vp, _vp, _vp,
                                   ctypes.c_size_t, _vp],
+    "houv_cd_reduce": [_vp, _vp, _ci, _ci, _ci, _cf, _vp, _vp, _vp, _vp],
     "houv_nn_search": [_vp, _vp, _ci, _ci, _ci, _vp, _vp, _vp],
     "houv_chamfer3d_backward": [_vp, _vp, _vp, _vp, _vp, _vp, _ci, _ci, _ci, _vp, _vp, _vp],
     "houv_kabsch": [_vp, _vp, _vp, _ci, _ci, _vp, _vp, _vp],

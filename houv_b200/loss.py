@@ -17,6 +17,8 @@ from .chamfer import cd, fscore
 
 
 def calc_cd(output, gt, calc_f1=False):
+    if not (torch.is_grad_enabled() and (output.requires_grad or gt.requires_grad)):
+        return calc_cd_fused(output, gt, calc_f1)  # evaluation: forward + one reduction launch
     cham_loss = cd()
     dist1, dist2, _, _ = cham_loss(gt, output)
     cd_p = (torch.sqrt(dist1).mean(1) + torch.sqrt(dist2).mean(1)) / 2
@@ -25,6 +27,23 @@ def calc_cd(output, gt, calc_f1=False):
         f1, _, _ = fscore(dist1, dist2)
         return cd_p, cd_t, f1
     return cd_p, cd_t
+
+
+def calc_cd_fused(output, gt, calc_f1=False, threshold=0.0001):
+    """calc_cd without autograd (the evaluation calls, e.g. completion/models/vrcnet.py:647):
+    Chamfer forward (K1) + houv_cd_reduce, two launches in all."""
+    from . import _lib
+    dist1, dist2, _, _ = cd()(gt.detach(), output.detach())
+    B, N = dist1.shape
+    M = dist2.shape[1]
+    out = torch.empty(3, B, device=dist1.device)
+    with torch.cuda.device(dist1.device):
+        rc = _lib.load().houv_cd_reduce(dist1.data_ptr(), dist2.data_ptr(), B, N, M, threshold,
+                                        out[0].data_ptr(), out[1].data_ptr(),
+                                        out[2].data_ptr() if calc_f1 else 0, _lib.stream_ptr())
+    _lib.check(rc, "houv_cd_reduce")
+    _lib.count_launches(1)
+    return (out[0], out[1], out[2]) if calc_f1 else (out[0], out[1])
 
 
 def calc_cd_percent(output, gt, calc_f1=False, percent=1):

@@ -17,6 +17,7 @@
  *   houv_chamfer3d_backward  <- chamfer_3D.backward chamfer_cuda.cpp:22-27,32
  *                               = chamfer_cuda_backward           chamfer3D.cu:176-195
  *   houv_nn_search           <- one NmDistanceKernel launch       chamfer3D.cu:12-134,142
+ *   houv_cd_reduce           <- calc_cd / fscore reductions      registration/model_utils_completion.py:69-80
  *   houv_kabsch              <- SVDHead.forward     registration/model_utils.py:220-255
  *   houv_icp                 <- o3d registration_icp call site    registration/train_ICP.py:148-151
  *   houv_pose_optimise       <- predict_model hot loop            registration/models/houv.py:106-138
@@ -70,6 +71,13 @@ int houv_nn_search(const float *query, const float *target, int B, int N, int M,
 int houv_chamfer3d_backward(const float *xyz1, const float *xyz2, const float *graddist1,
                             const float *graddist2, const int *idx1, const int *idx2, int B,
                             int N, int M, float *gradxyz1, float *gradxyz2, void *stream);
+
+/* Epilogue of calc_cd + fscore (model_utils_completion.py:69-80, utils/metrics/CD/fscore.py:3-16)
+ * on the outputs of a Chamfer forward: cd_p[B] = (mean sqrt dist1 + mean sqrt dist2)/2,
+ * cd_t[B] = mean dist1 + mean dist2, f1[B] (or NULL) = F-score at `threshold` (1e-4 in the
+ * reference), 0 where it is NaN.  Forward only. */
+int houv_cd_reduce(const float *dist1, const float *dist2, int B, int N, int M, float threshold,
+                   float *cd_p, float *cd_t, float *f1, void *stream);
 
 /* Fused multi-start pose optimisation (K3): `iters` iterations of
  *   HOUV.forward -> Predict_loss -> backward -> Adam.step      (houv.py:120-126)

@@ -52,11 +52,23 @@ def cd(input1, input2):
 
 
 # --------------------------------------------------------------- loss helpers
-def calc_cd(output, gt):
-    """model_utils_completion.py:69-80 (without f1)."""
+def fscore(dist1, dist2, threshold=0.0001):
+    """utils/metrics/CD/fscore.py:3-16."""
+    precision_1 = torch.mean((dist1 < threshold).float(), dim=1)
+    precision_2 = torch.mean((dist2 < threshold).float(), dim=1)
+    f = 2 * precision_1 * precision_2 / (precision_1 + precision_2)
+    f[torch.isnan(f)] = 0
+    return f, precision_1, precision_2
+
+
+def calc_cd(output, gt, calc_f1=False):
+    """model_utils_completion.py:69-80 = completion/model_utils.py:69-80."""
     dist1, dist2, _, _ = cd(gt, output)
     cd_p = (torch.sqrt(dist1).mean(1) + torch.sqrt(dist2).mean(1)) / 2
     cd_t = dist1.mean(1) + dist2.mean(1)
+    if calc_f1:
+        f1, _, _ = fscore(dist1, dist2)
+        return cd_p, cd_t, f1
     return cd_p, cd_t
 
 

@@ -159,6 +159,28 @@ def make_solve():
     print("solve fixtures written")
 
 
+def make_calccd():
+    """calccd_ref.npz: the reference's own calc_cd (model_utils_completion.py:69-80, identical to
+    completion/model_utils.py:69-80) with calc_f1, and the gradient of mean(cd_p)+mean(cd_t) with
+    respect to `output`, on a completion-shaped input (coarse output against a denser gt whose
+    points partly coincide with it, so the F-score threshold 1e-4 is exercised)."""
+    import torch
+    import ref_loader
+    muc = ref_loader.load()["muc"]
+    rng = np.random.RandomState(11)
+    gt = rng.rand(3, 500, 3).astype(np.float32)
+    out = gt[:, rng.permutation(500)[:200]] + (rng.rand(3, 200, 3) < 0.5) * \
+        rng.normal(0, 0.02, (3, 200, 3))
+    out = out.astype(np.float32)
+    o = torch.from_numpy(out).requires_grad_()
+    cd_p, cd_t, f1 = muc.calc_cd(o, torch.from_numpy(gt), calc_f1=True)
+    (cd_p.mean() + cd_t.mean()).backward()
+    np.savez_compressed(os.path.join(HERE, "calccd_ref.npz"), output=out, gt=gt,
+                        cd_p=cd_p.detach().numpy(), cd_t=cd_t.detach().numpy(), f1=f1.numpy(),
+                        grad_output=o.grad.numpy())
+    print("calc_cd fixtures written")
+
+
 def make_svd():
     """svdhead_ref.npz: the reference's SVDHead class (model_utils.py:213-255, source read
     and executed as-is) on noisy rigid correspondences, with and without weights, including
@@ -186,7 +208,7 @@ def make_svd():
     print("svd fixtures written")
 
 
-FAMILIES = {"chamfer": make_chamfer, "houv": make_houv, "svd": make_svd, "solve": make_solve}
+FAMILIES = {"chamfer": make_chamfer, "houv": make_houv, "svd": make_svd, "solve": make_solve, "calccd": make_calccd}
 
 if __name__ == "__main__":
     want = sys.argv[1:] or list(FAMILIES)

@@ -108,3 +108,18 @@ def test_solve_matches_reference_golden():
     assert _close(ans, g["solve_ans"], 1e-4)
     assert np.abs(ans[:, 3].numpy()).max() == 0
     assert _close(r_err, g["solve_r_err"], 1e-3) and _close(t_err, g["solve_t_err"], 1e-4)
+
+
+def test_calc_cd_with_fscore_matches_reference_golden():
+    """oracle calc_cd / fscore vs the reference's own (model_utils_completion.py:69-80,
+    fscore.py:3-16), values and the gradient of mean(cd_p)+mean(cd_t) w.r.t. the output cloud."""
+    g = load_npz("calccd_ref.npz")
+    o = torch.from_numpy(g["output"]).requires_grad_()
+    cd_p, cd_t, f1 = oh.calc_cd(o, torch.from_numpy(g["gt"]), calc_f1=True)
+    (cd_p.mean() + cd_t.mean()).backward()
+    assert _close(cd_p.detach(), g["cd_p"]) and _close(cd_t.detach(), g["cd_t"])
+    assert np.array_equal(f1.numpy(), g["f1"])
+    # coincident points (d = 0) make sqrt's backward 0 * inf = NaN in the reference: same places
+    got, ref = o.grad.numpy(), g["grad_output"]
+    assert np.isnan(ref).any() and np.array_equal(np.isnan(got), np.isnan(ref))
+    assert _close(np.nan_to_num(got), np.nan_to_num(ref), 1e-5)
