@@ -41,14 +41,17 @@ class _Chamfer3DModule:
         return 1
 
     @staticmethod
-    def backward(xyz1, xyz2, gradxyz1, gradxyz2, graddist1, graddist2, idx1, idx2):
+    def backward(xyz1, xyz2, gradxyz1, gradxyz2, graddist1, graddist2, idx1, idx2, assign=False):
+        """Accumulates into gradxyz1/gradxyz2 like the reference; assign=True (not in the reference)
+        writes them instead, so they may be torch.empty."""
         B, N, _ = xyz1.shape
         M = xyz2.shape[1]
+        lib = _lib.load()
+        fn = lib.houv_chamfer3d_backward_assign if assign else lib.houv_chamfer3d_backward
         with torch.cuda.device(xyz1.device):
-            rc = _lib.load().houv_chamfer3d_backward(
-                xyz1.data_ptr(), xyz2.data_ptr(), graddist1.data_ptr(), graddist2.data_ptr(),
-                idx1.data_ptr(), idx2.data_ptr(), B, N, M, gradxyz1.data_ptr(),
-                gradxyz2.data_ptr(), _lib.stream_ptr())
+            rc = fn(xyz1.data_ptr(), xyz2.data_ptr(), graddist1.data_ptr(), graddist2.data_ptr(),
+                    idx1.data_ptr(), idx2.data_ptr(), B, N, M, gradxyz1.data_ptr(),
+                    gradxyz2.data_ptr(), _lib.stream_ptr())
         _lib.check(rc, "houv_chamfer3d_backward")
         _lib.count_launches(1)
         return 1
@@ -91,9 +94,12 @@ class chamfer_3DFunction(Function):
         xyz1, xyz2, idx1, idx2 = ctx.saved_tensors
         graddist1 = graddist1.contiguous()
         graddist2 = graddist2.contiguous()
-        gradxyz1 = torch.zeros_like(xyz1)
-        gradxyz2 = torch.zeros_like(xyz2)
-        chamfer_3D.backward(xyz1, xyz2, gradxyz1, gradxyz2, graddist1, graddist2, idx1, idx2)
+        # the reference zero-fills and accumulates (:56-63); the assign entry point writes the
+        # gradient in the same launch
+        gradxyz1 = torch.empty_like(xyz1)
+        gradxyz2 = torch.empty_like(xyz2)
+        chamfer_3D.backward(xyz1, xyz2, gradxyz1, gradxyz2, graddist1, graddist2, idx1, idx2,
+                            assign=True)
         return gradxyz1, gradxyz2
 
 

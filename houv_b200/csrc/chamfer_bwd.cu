@@ -28,8 +28,7 @@ struct GradDir {
 };
 struct GradArgs {
     GradDir dir[2];
-    long long split;  // elements of direction 0 (= B*N)
-    long long total;  // B*(N+M)
+    long long items;  // B * ceil((N+M)/256) chunks of 256 points
     bool vec;         // both gradient buffers are 4-byte aligned at least (always) and the
                       // vector form is allowed (HOUV_K2_SCALAR unset)
 };
@@ -49,10 +48,20 @@ __device__ __forceinline__ void red3(float *o, float a, float b, float c, bool v
     }
 }
 
+// Work is ordered batch by batch: one item = 256 consecutive points of one batch element, direction
+// 0's N points first and direction 1's M points after them.  Both directions of a batch element hit
+// the same two gradient buffers (once as the owner's contiguous rows, once as the scatter target),
+// so keeping them adjacent in time makes the second touch an L2 hit instead of a second DRAM
+// read-modify-write (ncu, 6400 x 2048^2: 1.91 GB of DRAM traffic per launch before, see
+// profiles/r1_ncu_summary.md).
 __global__ void __launch_bounds__(256) grad_kernel(const GradArgs args) {
-    for (long long e = blockIdx.x * 256LL + threadIdx.x; e < args.total;
-         e += (long long)gridDim.x * 256) {
-        const bool second = e >= args.split;
+    const int per = args.dir[0].n + args.dir[0].m;  // points per batch element, both directions
+    const int chunks = (per + 255) >> 8;
+    for (long long item = blockIdx.x; item < args.items; item += gridDim.x) {
+        const long long bi = item / chunks;
+        const int r = (int)(item - bi * chunks) * 256 + threadIdx.x;
+        if (r >= per) continue;
+        const bool second = r >= args.dir[0].n;
         GradDir D;  // field-wise select keeps the argument struct out of local memory
         D.a = second ? args.dir[1].a : args.dir[0].a;
         D.b = second ? args.dir[1].b : args.dir[0].b;
@@ -62,8 +71,7 @@ __global__ void __launch_bounds__(256) grad_kernel(const GradArgs args) {
         D.gb = second ? args.dir[1].gb : args.dir[0].gb;
         D.n = second ? args.dir[1].n : args.dir[0].n;
         D.m = second ? args.dir[1].m : args.dir[0].m;
-        const long long w = second ? e - args.split : e;  // flat (batch, point)
-        const long long bi = w / D.n;
+        const long long w = bi * D.n + (second ? r - args.dir[0].n : r);  // flat (batch, point)
         const int j2 = D.idx[w];
         const float *pa = D.a + w * 3;
         const float *pb = D.b + (bi * D.m + j2) * 3;
@@ -78,28 +86,189 @@ __global__ void __launch_bounds__(256) grad_kernel(const GradArgs args) {
     }
 }
 
+// Batch-element-resident form: one CTA owns one batch element, stages both clouds in shared memory
+// (coalesced, 16-byte loads where the element is aligned), builds both gradient buffers there, and
+// adds the finished rows to the caller's buffers with one coalesced vector RED per 16 bytes.  Per
+// point that is 20 B read + 12 B of RED instead of 4 scattered RED packets through the L1->XBAR
+// port, which is what bounded grad_kernel (ncu: l1tex2xbar request cycles 78 % busy, DRAM 26 %).
+// Shared memory has no native float add (atomicAdd compiles to an LDS / FADD / ATOMS.CAST.SPIN loop),
+// which makes randomly addressed shared-memory wavefronts the next bound (ncu: l1tex data pipe 60-70 %).
+// Measured 6400 x 2048^2 on one B200: 305 us against 527 us streaming (DRAM traffic 1.12 GB per launch,
+// the 32 B/point floor plus the read half of the gradient read-modify-write).  A variant with the three
+// compare-and-swap chains of a point issued together was slower (450 us) and is not kept.  Needs 24*(N+M) bytes of shared memory.
+constexpr int kResThreads = 512;
+constexpr int kResPer = 4;  // points per thread and direction held in registers (clouds <= 2048)
+
+__device__ __forceinline__ void res_stage(float *dst, const float *src, int n3) {
+    if ((reinterpret_cast<uintptr_t>(src) & 15) == 0) {
+        const int q = n3 >> 2;
+        for (int i = threadIdx.x; i < q; i += kResThreads)
+            reinterpret_cast<float4 *>(dst)[i] = __ldg(reinterpret_cast<const float4 *>(src) + i);
+        for (int i = 4 * q + threadIdx.x; i < n3; i += kResThreads) dst[i] = __ldg(src + i);
+    } else {
+        for (int i = threadIdx.x; i < n3; i += kResThreads) dst[i] = __ldg(src + i);
+    }
+}
+
+// One point: v = 2*gd*(a_i - b_j) goes to the owner's row (+v) and to the partner's row (-v).
+__device__ __forceinline__ void res_point(const float *sa, const float *sb, float *ga, float *gb,
+                                          int i, int j, float g) {
+    const float v0 = __fmul_rn(g, __fsub_rn(sa[i * 3 + 0], sb[j * 3 + 0]));
+    const float v1 = __fmul_rn(g, __fsub_rn(sa[i * 3 + 1], sb[j * 3 + 1]));
+    const float v2 = __fmul_rn(g, __fsub_rn(sa[i * 3 + 2], sb[j * 3 + 2]));
+    atomicAdd(ga + i * 3 + 0, v0); atomicAdd(gb + j * 3 + 0, -v0);
+    atomicAdd(ga + i * 3 + 1, v1); atomicAdd(gb + j * 3 + 1, -v1);
+    atomicAdd(ga + i * 3 + 2, v2); atomicAdd(gb + j * 3 + 2, -v2);
+}
+
+__device__ __forceinline__ void res_dir(const float *sa, const float *sb, float *ga, float *gb,
+                                        const float *gd, const int *idx, int n) {
+    for (int i = threadIdx.x; i < n; i += kResThreads)
+        res_point(sa, sb, ga, gb, i, __ldg(idx + i), __fmul_rn(__ldg(gd + i), 2.f));
+}
+
+// assign = false: out += acc (the reference's accumulate-into contract); true: out = acc, which
+// spares the caller's zero-fill and the read half of the read-modify-write.
+__device__ __forceinline__ void res_flush(float *out, const float *acc, int n3, bool assign) {
+    if ((reinterpret_cast<uintptr_t>(out) & 15) == 0) {
+        const int q = n3 >> 2;
+        for (int i = threadIdx.x; i < q; i += kResThreads) {
+            const float4 v = *reinterpret_cast<const float4 *>(acc + 4 * i);
+            if (assign) reinterpret_cast<float4 *>(out)[i] = v;
+            else atomicAdd(reinterpret_cast<float4 *>(out) + i, v);
+        }
+        for (int i = 4 * q + threadIdx.x; i < n3; i += kResThreads) {
+            if (assign) out[i] = acc[i];
+            else atomicAdd(out + i, acc[i]);
+        }
+    } else {
+        for (int i = threadIdx.x; i < n3; i += kResThreads) {
+            if (assign) out[i] = acc[i];
+            else atomicAdd(out + i, acc[i]);
+        }
+    }
+}
+
+__global__ void __launch_bounds__(kResThreads, 2) grad_resident_kernel(const GradArgs args, int B,
+                                                                       bool assign) {
+    extern __shared__ __align__(16) float sm[];
+    const int n = args.dir[0].n, m = args.dir[0].m;
+    const int n3 = n * 3, m3 = m * 3;
+    const int n3p = (n3 + 3) & ~3, m3p = (m3 + 3) & ~3;  // keep every array 16-byte aligned
+    float *s1 = sm, *s2 = s1 + n3p, *g1 = s2 + m3p, *g2 = g1 + n3p;
+    const bool in_regs = n <= kResThreads * kResPer && m <= kResThreads * kResPer;
+    for (int bi = blockIdx.x; bi < B; bi += gridDim.x) {
+        const float *gd1 = args.dir[0].gd + (long long)bi * n, *gd2 = args.dir[1].gd + (long long)bi * m;
+        const int *ix1 = args.dir[0].idx + (long long)bi * n, *ix2 = args.dir[1].idx + (long long)bi * m;
+        // index / weight loads go out with the staging loads: one global round trip per element
+        int j1[kResPer], j2[kResPer];
+        float w1[kResPer], w2[kResPer];
+        if (in_regs) {
+#pragma unroll
+            for (int q = 0; q < kResPer; ++q) {
+                const int i = threadIdx.x + q * kResThreads;
+                j1[q] = i < n ? __ldg(ix1 + i) : 0;
+                w1[q] = i < n ? __ldg(gd1 + i) : 0.f;
+                j2[q] = i < m ? __ldg(ix2 + i) : 0;
+                w2[q] = i < m ? __ldg(gd2 + i) : 0.f;
+            }
+        }
+        res_stage(s1, args.dir[0].a + (long long)bi * n3, n3);
+        res_stage(s2, args.dir[0].b + (long long)bi * m3, m3);
+        for (int i = threadIdx.x; i < (n3p + m3p) >> 2; i += kResThreads)
+            reinterpret_cast<float4 *>(g1)[i] = make_float4(0.f, 0.f, 0.f, 0.f);  // g1 and g2
+        __syncthreads();
+        if (in_regs) {
+#pragma unroll
+            for (int q = 0; q < kResPer; ++q) {
+                const int i = threadIdx.x + q * kResThreads;
+                if (i < n) res_point(s1, s2, g1, g2, i, j1[q], __fmul_rn(w1[q], 2.f));
+                if (i < m) res_point(s2, s1, g2, g1, i, j2[q], __fmul_rn(w2[q], 2.f));
+            }
+        } else {
+            res_dir(s1, s2, g1, g2, gd1, ix1, n);
+            res_dir(s2, s1, g2, g1, gd2, ix2, m);
+        }
+        __syncthreads();
+        res_flush(args.dir[0].ga + (long long)bi * n3, g1, n3, assign);
+        res_flush(args.dir[0].gb + (long long)bi * m3, g2, m3, assign);
+        __syncthreads();
+    }
+}
+
 }  // namespace houv
 
 using namespace houv;
 
-extern "C" int houv_chamfer3d_backward(const float *xyz1, const float *xyz2,
-                                       const float *graddist1, const float *graddist2,
-                                       const int *idx1, const int *idx2, int B, int N, int M,
-                                       float *gradxyz1, float *gradxyz2, void *stream) {
+static int backward_impl(const float *xyz1, const float *xyz2, const float *graddist1,
+                         const float *graddist2, const int *idx1, const int *idx2, int B, int N,
+                         int M, float *gradxyz1, float *gradxyz2, bool assign, void *stream) {
     if (B < 0 || N < 0 || M < 0) return HOUV_E_BADARG;
+    if (assign && B > 0) {  // an empty partner cloud leaves a zero gradient
+        if ((N > 0 && !gradxyz1) || (M > 0 && !gradxyz2)) return HOUV_E_BADARG;
+        if (N == 0 || M == 0) {
+            cudaError_t e = cudaSuccess;
+            if (N > 0) e = cudaMemsetAsync(gradxyz1, 0, sizeof(float) * 3 * (size_t)B * N, (cudaStream_t)stream);
+            if (M > 0) e = cudaMemsetAsync(gradxyz2, 0, sizeof(float) * 3 * (size_t)B * M, (cudaStream_t)stream);
+            return (int)e;
+        }
+    }
     if (B == 0 || N == 0 || M == 0) return 0;  // nothing to gather from: grads stay zero
     if (!xyz1 || !xyz2 || !graddist1 || !graddist2 || !idx1 || !idx2 || !gradxyz1 || !gradxyz2)
         return HOUV_E_BADARG;
     GradArgs a;
     a.dir[0] = GradDir{xyz1, xyz2, graddist1, idx1, gradxyz1, gradxyz2, N, M};
     a.dir[1] = GradDir{xyz2, xyz1, graddist2, idx2, gradxyz2, gradxyz1, M, N};
-    a.split = (long long)B * N;
-    a.total = (long long)B * ((long long)N + M);
+    if ((long long)N + M > 0x7fffff00LL) return HOUV_E_BADARG;
+    a.items = (long long)B * (((long long)N + M + 255) / 256);
     static const bool scalar_only = getenv("HOUV_K2_SCALAR") != nullptr;
     a.vec = !scalar_only;
-    long long blocks = (a.total + 255) / 256;
+    // HOUV_K2_VARIANT: 0 = streaming grad_kernel, 1 = batch-element-resident kernel where it fits,
+    // unset = resident when there are enough batch elements to fill the GPU.
+    const int forced = getenv("HOUV_K2_VARIANT") ? atoi(getenv("HOUV_K2_VARIANT")) : -1;
+    const size_t res_bytes = 2 * sizeof(float) * ((((size_t)N * 3 + 3) & ~(size_t)3) +
+                                                  (((size_t)M * 3 + 3) & ~(size_t)3));
+    const bool fits = res_bytes <= 200 * 1024;
+    if (fits && (forced >= 1 || (forced < 0 && B >= 148))) {
+        const int per_sm = (int)((227 * 1024) / (res_bytes + 1024));
+        int grid = 148 * (per_sm < 1 ? 1 : per_sm > 2 ? 2 : per_sm);  // registers allow 2 x 512 threads
+        if (grid > B) grid = B;
+        static bool attr_set = false;
+        if (!attr_set) {
+            cudaError_t e = cudaFuncSetAttribute(grad_resident_kernel,
+                                                 cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                 200 * 1024);
+            if (e != cudaSuccess) return (int)e;
+            attr_set = true;
+        }
+        grad_resident_kernel<<<grid, kResThreads, res_bytes, (cudaStream_t)stream>>>(a, B, assign);
+        return check_launch();
+    }
+    if (assign) {  // the streaming kernel accumulates: zero-fill here, on the same stream
+        cudaError_t e = cudaMemsetAsync(gradxyz1, 0, sizeof(float) * 3 * (size_t)B * N, (cudaStream_t)stream);
+        if (e == cudaSuccess)
+            e = cudaMemsetAsync(gradxyz2, 0, sizeof(float) * 3 * (size_t)B * M, (cudaStream_t)stream);
+        if (e != cudaSuccess) return (int)e;
+    }
+    long long blocks = a.items;
     const long long cap = 148LL * 8 * 4;  // grid-stride beyond a few waves
     if (blocks > cap) blocks = cap;
     grad_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(a);
     return check_launch();
+}
+
+extern "C" int houv_chamfer3d_backward(const float *xyz1, const float *xyz2,
+                                       const float *graddist1, const float *graddist2,
+                                       const int *idx1, const int *idx2, int B, int N, int M,
+                                       float *gradxyz1, float *gradxyz2, void *stream) {
+    return backward_impl(xyz1, xyz2, graddist1, graddist2, idx1, idx2, B, N, M, gradxyz1, gradxyz2,
+                         false, stream);
+}
+
+extern "C" int houv_chamfer3d_backward_assign(const float *xyz1, const float *xyz2,
+                                              const float *graddist1, const float *graddist2,
+                                              const int *idx1, const int *idx2, int B, int N, int M,
+                                              float *gradxyz1, float *gradxyz2, void *stream) {
+    return backward_impl(xyz1, xyz2, graddist1, graddist2, idx1, idx2, B, N, M, gradxyz1, gradxyz2,
+                         true, stream);
 }

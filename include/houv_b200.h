@@ -16,6 +16,7 @@
  *                               = chamfer_cuda_forward            chamfer3D.cu:136-154
  *   houv_chamfer3d_backward  <- chamfer_3D.backward chamfer_cuda.cpp:22-27,32
  *                               = chamfer_cuda_backward           chamfer3D.cu:176-195
+ *   houv_chamfer3d_backward_assign <- chamfer_3DFunction.backward's zero-fill + backward  dist_chamfer_3D.py:56-63
  *   houv_nn_search           <- one NmDistanceKernel launch       chamfer3D.cu:12-134,142
  *   houv_cd_reduce           <- calc_cd / fscore reductions      registration/model_utils_completion.py:69-80
  *   houv_kabsch              <- SVDHead.forward     registration/model_utils.py:220-255
@@ -71,6 +72,14 @@ int houv_nn_search(const float *query, const float *target, int B, int N, int M,
 int houv_chamfer3d_backward(const float *xyz1, const float *xyz2, const float *graddist1,
                             const float *graddist2, const int *idx1, const int *idx2, int B,
                             int N, int M, float *gradxyz1, float *gradxyz2, void *stream);
+
+/* The same gradient WRITTEN to gradxyz1/gradxyz2 (buffers may arrive uninitialised): what
+ * chamfer_3DFunction.backward computes after its own zero-fill (dist_chamfer_3D.py:56-63), without the
+ * separate fill pass.  Large batches of clouds that fit one SM's shared memory (24*(N+M) bytes <= 200 KB)
+ * are stored directly; other shapes are zero-filled on `stream` and accumulated as above. */
+int houv_chamfer3d_backward_assign(const float *xyz1, const float *xyz2, const float *graddist1,
+                                   const float *graddist2, const int *idx1, const int *idx2, int B,
+                                   int N, int M, float *gradxyz1, float *gradxyz2, void *stream);
 
 /* Epilogue of calc_cd + fscore (model_utils_completion.py:69-80, utils/metrics/CD/fscore.py:3-16)
  * on the outputs of a Chamfer forward: cd_p[B] = (mean sqrt dist1 + mean sqrt dist2)/2,

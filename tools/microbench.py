@@ -59,7 +59,7 @@ def cmd_chamfer():
     peak = fp32_peak(0)["tflops_best"]
     print(json.dumps({"fp32_peak_tflops": peak}))
     for name, (B, N, M) in {"C2": (32, 2048, 2048), "C5": (64, 16384, 2048),
-                            "unit_timing": (32, 2000, 1000), "B1": (1, 2048, 2048),
+                            "unit_timing": (32, 2000, 1000), "B1": (1, 2048, 2048), "rows592": (592, 2048, 2048),
                             "rows6400": (6400, 2048, 2048)}.items():
         torch.manual_seed(0)
         x1 = torch.rand(B, N, 3, device="cuda")
@@ -85,6 +85,15 @@ def cmd_chamfer():
         byts = 32.0 * B * (N + M)
         print(json.dumps({"case": name, "kernel": "K2 bwd", "ms_median": round(med, 4),
                           "GBps": round(byts / med / 1e6, 1)}))
+        # what autograd pays: zero-fill + accumulate (the reference's scheme) against the assign entry
+        def zero_then_accumulate():
+            g1.zero_(); g2.zero_()
+            chamfer_3D.backward(x1, x2, g1, g2, gd1, gd2, i1, i2)
+        med_z, _ = timeit(zero_then_accumulate, flush=flush)
+        med_a, _ = timeit(lambda: chamfer_3D.backward(x1, x2, g1, g2, gd1, gd2, i1, i2, assign=True),
+                          flush=flush)
+        print(json.dumps({"case": name, "kernel": "K2 bwd", "zero_fill_plus_accumulate_ms": round(med_z, 4),
+                          "assign_ms": round(med_a, 4), "assign_GBps": round(byts / med_a / 1e6, 1)}))
 
 
 def cmd_refext():
