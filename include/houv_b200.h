@@ -20,6 +20,7 @@
  *   houv_nn_search           <- one NmDistanceKernel launch       chamfer3D.cu:12-134,142
  *   houv_cd_reduce           <- calc_cd / fscore reductions      registration/model_utils_completion.py:69-80
  *   houv_kabsch              <- SVDHead.forward     registration/model_utils.py:220-255
+ *   houv_idam_step           <- IDAM refinement iteration tail     registration/models/idam.py:317-342
  *   houv_icp                 <- o3d registration_icp call site    registration/train_ICP.py:148-151
  *   houv_pose_optimise       <- predict_model hot loop            registration/models/houv.py:106-138
  */
@@ -151,6 +152,18 @@ int houv_pose_optimise_ex(const HouvPoseProblem *problem, void *stream);
  *                                det(V U^T) < 0 (:236-239); t = -R mean(src) + mean(corr) */
 int houv_kabsch(const float *src, const float *src_corr, const float *weights, int B, int N,
                 float *R, float *t, void *stream);
+
+/* One refinement step of IDAM's iterative weighted Kabsch, fused (K6; registration/models/idam.py:317-342):
+ *   src[B,3,N], tgt[B,3,M] channel-first; corr_idx[B,N] (int32, or int64 when corr_is_int64 != 0) indexes
+ *   tgt columns and must lie in [0,M); weight_logits[B,N] are the soft-elimination scores BEFORE the sigmoid.
+ *   w = sigmoid(logits); w *= (w >= median(w)) [lower median, as torch.median]; w /= sum(w) + 1e-8   (:329-331)
+ *   R_ab, t_ab = SVDHead(src, tgt[:, :, corr_idx], w)                              (:318, :335, idam.py:157-189)
+ *   src_out = R_ab src + t_ab;  R_acc <- R_ab R_acc;  t_acc <- R_ab t_acc + t_ab   (:338-340)
+ * src_out[B,3,N], R_acc[B,9]/t_acc[B,3] (updated in place, both or neither), R_ab[B,9], t_ab[B,3] and
+ * weights_out[B,N] may each be NULL.  N <= 8192 (HOUV_E_TOOBIG above). */
+int houv_idam_step(const float *src, const float *tgt, const void *corr_idx, int corr_is_int64,
+                   const float *weight_logits, int B, int N, int M, float *src_out, float *R_acc,
+                   float *t_acc, float *R_ab, float *t_ab, float *weights_out, void *stream);
 
 /* Point-to-point ICP, one CTA per pair (train_ICP.py:148-151 call site; Open3D 0.9.0
  * algorithm restated, see csrc/icp.cu).

@@ -406,6 +406,23 @@ class SVDHead(nn.Module):
         return R, t.view(src.size(0), 3)
 
 
+def idam_step(src, tgt, corr_idx, weight_logits, R, t, head=None):
+    """The tail of one iteration of IDAM.forward (registration/models/idam.py:317-342), torch CPU:
+    correspondences by index (:318), hybrid point elimination (:329-331), weighted SVDHead (:335),
+    move src and compose the running pose (:338-340).  `head` = the SVD head to use (the reference's
+    own class when making golden vectors, ours above otherwise)."""
+    head = head or SVDHead()
+    src_corr = tgt[np.arange(tgt.size(0))[:, np.newaxis], :, corr_idx].transpose(1, 2)
+    weights = torch.sigmoid(weight_logits)
+    weights = weights * (weights >= weights.median(-1, keepdim=True)[0]).float()
+    weights = weights / (weights.sum(-1, keepdim=True) + 1e-8)
+    rotation_ab, translation_ab = head(src, src_corr, weights.unsqueeze(1))
+    src = torch.matmul(rotation_ab, src) + translation_ab.unsqueeze(-1)
+    R = torch.matmul(rotation_ab, R)
+    t = torch.matmul(rotation_ab, t.unsqueeze(-1)).squeeze(-1) + translation_ab
+    return src, R, t, rotation_ab, translation_ab, weights
+
+
 # ------------------------------------------------------------------------ ICP
 def icp_point_to_point(source, target, max_distance=0.02, init=None, max_iteration=500,
                        relative_fitness=1e-6, relative_rmse=1e-6):

@@ -208,7 +208,53 @@ def make_svd():
     print("svd fixtures written")
 
 
-FAMILIES = {"chamfer": make_chamfer, "houv": make_houv, "svd": make_svd, "solve": make_solve, "calccd": make_calccd}
+def make_idam():
+    """idam_ref.npz: three chained refinement steps (idam.py:317-342) with the reference's own IDAM
+    SVDHead class (models/idam.py:150-189, source read and executed as-is); correspondences are the
+    true ones with a fraction scrambled, logits favour the true ones; even and odd N (median rule)."""
+    import torch
+    import ref_loader
+    sys.path.insert(0, os.path.dirname(os.path.dirname(HERE)))
+    from oracle import houv as oh
+
+    class Args:
+        use_fpfh = False
+        descriptor_size = 8
+    head = ref_loader.load_svdhead("models/idam.py")(Args())
+    out = {}
+    for tag, (B, N, M) in {"even": (5, 128, 160), "odd": (3, 77, 77)}.items():
+        torch.manual_seed(N)
+        src = torch.randn(B, 3, N) * 0.3
+        Rg = torch.linalg.qr(torch.randn(B, 3, 3))[0]
+        Rg = Rg * torch.sign(torch.det(Rg)).reshape(B, 1, 1)
+        tgt = torch.randn(B, 3, M) * 0.3
+        perm = torch.stack([torch.randperm(M)[:N] for _ in range(B)])
+        moved = Rg @ src + torch.randn(B, 3, 1) * 0.1 + 0.003 * torch.randn(B, 3, N)
+        tgt[torch.arange(B)[:, None], :, perm] = moved.transpose(1, 2)
+        R = torch.eye(3).repeat(B, 1, 1)
+        t = torch.zeros(B, 3)
+        cur = src
+        for it in range(3):
+            corr = perm.clone()
+            bad = torch.rand(B, N) < 0.3
+            corr[bad] = torch.randint(0, M, (int(bad.sum()),))
+            logits = torch.randn(B, N) + 2.0 * (~bad).float()
+            if it == 1:
+                logits[:, : N // 3] = 0.25  # ties at and around the median
+            out["%s_src%d" % (tag, it)] = cur.numpy()
+            out["%s_corr%d" % (tag, it)] = corr.numpy()
+            out["%s_logits%d" % (tag, it)] = logits.numpy()
+            out["%s_Rin%d" % (tag, it)] = R.numpy()
+            out["%s_tin%d" % (tag, it)] = t.numpy()
+            cur, R, t, Rab, tab, w = oh.idam_step(cur, tgt, corr, logits, R, t, head=head)
+            for k, v in dict(out=cur, R=R, t=t, Rab=Rab, tab=tab, w=w).items():
+                out["%s_%s%d" % (tag, k, it)] = v.numpy()
+        out[tag + "_tgt"] = tgt.numpy()
+    np.savez_compressed(os.path.join(HERE, "idam_ref.npz"), **out)
+    print("idam fixtures written")
+
+
+FAMILIES = {"idam": make_idam, "chamfer": make_chamfer, "houv": make_houv, "svd": make_svd, "solve": make_solve, "calccd": make_calccd}
 
 if __name__ == "__main__":
     want = sys.argv[1:] or list(FAMILIES)

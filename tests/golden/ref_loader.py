@@ -104,11 +104,11 @@ def load():
     return _loaded
 
 
-def load_svdhead():
-    """registration/model_utils.py imports open3d & co. at the top; SVDHead only
-    needs torch, so exec the class source alone (text is read, not copied)."""
+def load_svdhead(rel="model_utils.py"):
+    """registration/model_utils.py (and models/idam.py) import open3d & co. at the top; SVDHead
+    only needs torch, so exec the class source alone (text is read, not copied)."""
     import ast
-    src = open(os.path.join(REG, "model_utils.py")).read()
+    src = open(os.path.join(REG, rel)).read()
     tree = ast.parse(src)
     node = [n for n in tree.body if isinstance(n, ast.ClassDef) and n.name == "SVDHead"][0]
     ns = {"torch": torch, "nn": torch.nn}

@@ -123,3 +123,16 @@ def test_calc_cd_with_fscore_matches_reference_golden():
     got, ref = o.grad.numpy(), g["grad_output"]
     assert np.isnan(ref).any() and np.array_equal(np.isnan(got), np.isnan(ref))
     assert _close(np.nan_to_num(got), np.nan_to_num(ref), 1e-5)
+
+
+def test_idam_step_restatement_matches_reference_golden():
+    """oracle.idam_step with the oracle's own SVDHead reproduces the vectors made with the reference's IDAM
+    SVDHead class (tests/golden/make_golden.py idam)."""
+    g = load_npz("idam_ref.npz")
+    for tag in ("even", "odd"):
+        tgt = torch.from_numpy(g[tag + "_tgt"])
+        for it in range(3):
+            k = lambda n: torch.from_numpy(g["%s_%s%d" % (tag, n, it)])
+            got = oh.idam_step(k("src"), tgt, k("corr"), k("logits"), k("Rin"), k("tin"))
+            for name, v in zip(("out", "R", "t", "Rab", "tab", "w"), got):
+                assert torch.allclose(v, k(name), atol=1e-6), (tag, it, name)

@@ -265,6 +265,25 @@ def cmd_icp():
                       "cpu_oracle_pairs_per_s": round(1.0 / cpu, 2)}))
 
 
+def cmd_idam():
+    """K6 (houv_idam_step) beside the same iteration tail in torch ops on the same GPU (the oracle's
+    restatement of idam.py:317-342 run on CUDA tensors, i.e. the reference's own execution scheme:
+    ~15 launches plus a per-sample torch.svd loop with a host-synchronising `if`)."""
+    from houv_b200.kabsch import idam_step
+    from oracle import houv as oh
+    for B, N in ((32, 128), (32, 1024), (256, 128)):
+        torch.manual_seed(0)
+        src, tgt = torch.randn(B, 3, N).cuda() * 0.3, torch.randn(B, 3, N).cuda() * 0.3
+        corr = torch.randint(0, N, (B, N)).cuda()
+        logits = torch.randn(B, N).cuda()
+        R0, t0 = torch.eye(3).repeat(B, 1, 1).cuda(), torch.zeros(B, 3).cuda()
+        med, _ = timeit(lambda: idam_step(src, tgt, corr, logits, R0, t0), iters=20)
+        head = oh.SVDHead().cuda()
+        ref, _ = timeit(lambda: oh.idam_step(src, tgt, corr, logits, R0, t0, head=head), iters=3, warmup=1)
+        print(json.dumps({"kernel": "K6 idam_step", "B": B, "N": N, "ms": round(med, 4),
+                          "torch_ops_same_gpu_ms": round(ref, 3), "ratio": round(ref / med, 1)}))
+
+
 def cmd_pose():
     """K3 at the BASELINE shape: P pairs x 64 starts x `iters` iterations, 2048 points."""
     import numpy as np
@@ -302,4 +321,4 @@ def cmd_pose():
 
 
 if __name__ == "__main__":
-    {"probe": cmd_probe, "chamfer": cmd_chamfer, "pose": cmd_pose, "refext": cmd_refext, "icp": cmd_icp, "solve": cmd_solve, "refhouv": cmd_refhouv}[sys.argv[1] if len(sys.argv) > 1 else "probe"]()
+    {"probe": cmd_probe, "chamfer": cmd_chamfer, "pose": cmd_pose, "refext": cmd_refext, "icp": cmd_icp, "solve": cmd_solve, "refhouv": cmd_refhouv, "idam": cmd_idam}[sys.argv[1] if len(sys.argv) > 1 else "probe"]()
