@@ -41,6 +41,8 @@ _SIGNATURES = {
     "houv_cd_reduce": [_vp, _vp, _ci, _ci, _ci, _cf, _vp, _vp, _vp, _vp],
     "houv_nn_search": [_vp, _vp, _ci, _ci, _ci, _vp, _vp, _vp],
     "houv_chamfer3d_backward": [_vp, _vp, _vp, _vp, _vp, _vp, _ci, _ci, _ci, _vp, _vp, _vp],
+    "houv_emd_forward": [_vp, _vp, _ci, _ci, ctypes.c_float, _ci, _vp, _vp, _vp, _vp, ctypes.c_size_t, _vp],
+    "houv_emd_backward": [_vp, _vp, _vp, _vp, _ci, _ci, _vp, _vp],
     "houv_idam_step": [_vp, _vp, _vp, _ci, _vp, _ci, _ci, _ci, _vp, _vp, _vp, _vp, _vp, _vp, _vp],
     "houv_chamfer3d_backward_assign": [_vp, _vp, _vp, _vp, _vp, _vp, _ci, _ci, _ci, _vp, _vp, _vp],
     "houv_kabsch": [_vp, _vp, _vp, _ci, _ci, _vp, _vp, _vp],
@@ -55,7 +57,8 @@ _SIGNATURES = {
     "houv_fp32_probe": [_vp, _ci, _ci, ctypes.POINTER(ctypes.c_double), _vp],
 }
 
-EXPORTS = tuple(_SIGNATURES) + ("houv_version", "houv_chamfer3d_workspace_bytes")
+EXPORTS = tuple(_SIGNATURES) + ("houv_version", "houv_chamfer3d_workspace_bytes",
+                                   "houv_emd_workspace_bytes")
 
 
 def lib_path():
@@ -74,6 +77,8 @@ def load():
             fn.restype = _ci
         lib.houv_chamfer3d_workspace_bytes.restype = ctypes.c_size_t
         lib.houv_chamfer3d_workspace_bytes.argtypes = [_ci, _ci, _ci]
+        lib.houv_emd_workspace_bytes.restype = ctypes.c_size_t
+        lib.houv_emd_workspace_bytes.argtypes = [_ci, _ci]
         lib.houv_version.restype = ctypes.c_char_p
         lib.houv_version.argtypes = []
         _LIB = lib

@@ -1,0 +1,282 @@
+// K7 -- EMD approximation (auction algorithm), all iterations in ONE launch, for sm_100a.
+//
+// Replaces emd_cuda_forward / emd_cuda_backward
+// (/root/reference/utils/metrics/EMD/emd_cuda.cu:230-316; wrapper emd_module.py:40-90).  The reference
+// launches seven kernels per iteration (clear, calc_unass_cnt, calc_unass_cnt_sum, calc_unass_idx, Bid,
+// GetMax, Assign; :253-264) with every array in global memory; evaluation runs use 3000 iterations
+// (registration/models/pcn.py:169), almost all of them with a handful of unassigned points, so the
+// reference's cost is launch latency x 7 x iters.  Here one CTA owns one batch element for the whole
+// auction: prices, bids, both assignment maps, the unassigned list and the target cloud (SoA) stay in
+// shared memory (44 B per point, n <= 4096; larger clouds use a caller-provided global workspace through
+// the same code, compiled a second time for generic addresses), phases are separated by __syncthreads() instead of launches, and the loop ends as
+// soon as nothing is unassigned (the reference's remaining iterations are no-ops).
+//
+// Arithmetic is the reference's as nvcc compiles it (SASS of the reference extension, sm_100a):
+//   value(k) = (float)((3.0 - (double)sqrtf(fma(dz,dz,fma(dx,dx,dy*dy)))) - (double)price[k])   (:140-144)
+//   increment = (best - better) + eps (float, :175);  GetMax compares in double with +-1e-6 (:187)
+//   dist = fma(dz,dz,fma(dx,dx,dy*dy)) (:222-226)
+// The two places where the reference's result depends on scheduling are fixed the same way as in
+// oracle/emd_oracle.c: equal values -> lowest k; bidders within 1e-6 of an object's maximum -> lowest j.
+#include <limits.h>
+
+#include "common.cuh"
+
+namespace houv {
+
+constexpr int kEmdThreads = 1024;
+constexpr int kEmdSmemN = 4096;   // 44 B/point of state in shared memory up to here
+
+struct EmdArgs {
+    const float *xyz1, *xyz2;
+    float *dist;
+    int *assignment;
+    int *iters_used;   // [B] or null
+    unsigned *ws;      // global state, 11*n words per batch element, when n > kEmdSmemN
+    int B, n, iters;
+    float eps;
+};
+
+struct Top2 {
+    float best, better;
+    int i;
+};
+
+// winner = larger value, lower index on equal values; better = max(winner's better, loser's best)
+__device__ __forceinline__ Top2 merge(const Top2 &a, const Top2 &b) {
+    const bool b_wins = b.best > a.best || (b.best == a.best && (unsigned)b.i < (unsigned)a.i);
+    Top2 r;
+    r.best = b_wins ? b.best : a.best;
+    r.i = b_wins ? b.i : a.i;
+    r.better = b_wins ? fmaxf(b.better, a.best) : fmaxf(a.better, b.best);
+    return r;
+}
+
+// State of one batch element, 11 words per point: pts[n] = (x, y, z, price) of the target cloud and its
+// prices packed so that one 16-byte load feeds a candidate evaluation, then max_inc, bid_inc, max_idx,
+// ainv, asg, bid, list.  kSmem: the block lives in dynamic shared memory (pointers provably shared, so
+// LDS/STS/ATOMS); otherwise in the caller's workspace.
+template <bool kSmem>
+__global__ void __launch_bounds__(kEmdThreads, 1) emd_auction_kernel(const EmdArgs A) {
+    extern __shared__ __align__(16) unsigned sm_u[];
+    __shared__ int s_cnt;
+    __shared__ Top2 s_merge[kEmdThreads / 32];
+    const int n = A.n, tid = threadIdx.x;
+    for (int b = blockIdx.x; b < A.B; b += gridDim.x) {
+        unsigned *base = kSmem ? sm_u : A.ws + (size_t)b * ((11 * (size_t)n + 3) & ~(size_t)3);  // 16-byte aligned
+        float4 *pts = reinterpret_cast<float4 *>(base);
+        float *max_inc = reinterpret_cast<float *>(base + 4 * (size_t)n);
+        float *bid_inc = max_inc + n;
+        int *max_idx = reinterpret_cast<int *>(bid_inc + n);
+        int *ainv = max_idx + n;
+        int *asg = ainv + n;
+        int *bid = asg + n;
+        int *list = bid + n;
+        const float *x1 = A.xyz1 + (size_t)b * n * 3;
+        const float *x2g = A.xyz2 + (size_t)b * n * 3;
+        __syncthreads();
+        for (int k = tid; k < n; k += kEmdThreads) {
+            pts[k] = make_float4(x2g[3 * k], x2g[3 * k + 1], x2g[3 * k + 2], 0.f);
+            max_inc[k] = 0.f; max_idx[k] = INT_MAX; ainv[k] = -1; asg[k] = -1;
+        }
+        int used = 0;
+        for (int it = 0; it < A.iters; ++it) {
+            const bool last = it == A.iters - 1;
+            if (tid == 0) s_cnt = 0;
+            __syncthreads();
+            for (int j = tid; j < n; j += kEmdThreads)
+                if (asg[j] == -1) list[atomicAdd(&s_cnt, 1)] = j;
+            __syncthreads();
+            const int U = s_cnt;
+            if (U == 0) break;
+            ++used;
+            // ---- Bid: G threads per unassigned point (power of two), strided over the candidates
+            int G = 1;
+            while (G * 2 * U <= kEmdThreads) G *= 2;
+            const int groups = kEmdThreads / G;
+            const int lane_g = tid & (G - 1);
+            for (int p0 = 0; p0 < U; p0 += groups) {
+                const int p = p0 + tid / G;
+                const bool valid = p < U;
+                const int j = valid ? list[p] : 0;
+                Top2 t{-1e9f, -1e9f, -1};
+                float px = 0.f, py = 0.f, pz = 0.f;
+                const int w = G < 32 ? G : 32;  // lanes of this warp that serve the same bidder
+                // First candidate of every lane, exactly; the second best of those w values is a lower bound
+                // of the bidder's final second best and becomes the lanes' common pruning threshold (a lane
+                // that only sees n/G candidates would otherwise never build a useful one of its own).
+                if (valid) {
+                    px = __ldg(x1 + 3 * j); py = __ldg(x1 + 3 * j + 1); pz = __ldg(x1 + 3 * j + 2);
+                    if (lane_g < n) {
+                        const float4 c = pts[lane_g];
+                        const float dx = __fsub_rn(c.x, px), dy = __fsub_rn(c.y, py), dz = __fsub_rn(c.z, pz);
+                        const float sq = __fmaf_rn(dz, dz, __fmaf_rn(dx, dx, __fmul_rn(dy, dy)));
+                        t.best = (float)((3.0 - (double)__fsqrt_rn(sq)) - (double)c.w);
+                        t.i = lane_g;
+                    }
+                }
+                float shared_better = -1e9f;
+                if (w > 1) {
+                    Top2 g = t;
+                    for (int o = w >> 1; o > 0; o >>= 1) {
+                        Top2 u;
+                        u.best = __shfl_xor_sync(0xffffffffu, g.best, o);
+                        u.better = __shfl_xor_sync(0xffffffffu, g.better, o);
+                        u.i = __shfl_xor_sync(0xffffffffu, g.i, o);
+                        g = merge(g, u);
+                    }
+                    shared_better = g.better;
+                }
+                if (valid) {
+                    // A candidate whose value is certainly below a lower bound of the bidder's final second
+                    // best (this lane's running one, or the common one above) cannot be among its two best,
+                    // so it is dropped on the squared distance alone: value < bound  <=>  sqrt(sq) > 3 - bound
+                    // - price, tested with a margin 16x the rounding of the quantities involved.  That keeps
+                    // the square root, the two float->double conversions, the double subtractions and the
+                    // conversion back (XU / FP64 pipes) off all but the few candidates that can matter.
+                    float bound = shared_better;  // -1e9 keeps everything
+                    float fa = 3.f - bound;
+                    float fb = fa + 0x1p-20f * (fabsf(fa) + fabsf(bound) + 4.f);
+#pragma unroll 2
+                    for (int k = lane_g + G; k < n; k += G) {
+                        const float4 c = pts[k];
+                        const float dx = __fsub_rn(c.x, px), dy = __fsub_rn(c.y, py), dz = __fsub_rn(c.z, pz);
+                        const float sq = __fmaf_rn(dz, dz, __fmaf_rn(dx, dx, __fmul_rn(dy, dy)));
+                        const float th = fmaf(c.w, -(1.f - 0x1p-20f), fb);  // 3 - bound - price + margin
+                        if (th <= 0.f || sq > th * th) continue;
+                        const float d = (float)((3.0 - (double)__fsqrt_rn(sq)) - (double)c.w);
+                        if (d > t.best) { t.better = t.best; t.best = d; t.i = k; }
+                        else if (d > t.better) t.better = d;
+                        else continue;
+                        if (t.better > bound) {
+                            bound = t.better;
+                            fa = 3.f - bound;
+                            fb = fa + 0x1p-20f * (fabsf(fa) + fabsf(bound) + 4.f);
+                        }
+                    }
+                }
+                for (int o = w >> 1; o > 0; o >>= 1) {
+                    Top2 u;
+                    u.best = __shfl_xor_sync(0xffffffffu, t.best, o);
+                    u.better = __shfl_xor_sync(0xffffffffu, t.better, o);
+                    u.i = __shfl_xor_sync(0xffffffffu, t.i, o);
+                    t = merge(t, u);
+                }
+                if (G > 32) {  // uniform across the CTA: G depends on U only
+                    if ((tid & 31) == 0) s_merge[tid >> 5] = t;
+                    __syncthreads();
+                    if (lane_g == 0) {
+                        const int w0 = tid >> 5;
+                        for (int q = 1; q < G / 32; ++q) t = merge(t, s_merge[w0 + q]);
+                    }
+                    __syncthreads();
+                }
+                if (valid && lane_g == 0) {
+                    const float inc = __fadd_rn(__fsub_rn(t.best, t.better), A.eps);
+                    bid[j] = t.i;
+                    bid_inc[j] = inc;
+                    // float max through the signed-int order: increments are >= 0, the cleared
+                    // value -1e9 is negative (emd_cuda.cu:10-20 is the same max)
+                    atomicMax(reinterpret_cast<int *>(max_inc) + t.i, __float_as_int(inc));
+                }
+            }
+            __syncthreads();
+            // ---- GetMax (:181-194): lowest j among the bidders within 1e-6 of the object's maximum
+            for (int p = tid; p < U; p += kEmdThreads) {
+                const int j = list[p], o = bid[j];
+                const double bi = (double)bid_inc[j], mx = (double)max_inc[o];
+                if (bi - 1e-6 <= mx && mx <= bi + 1e-6) atomicMin(max_idx + o, j);
+            }
+            __syncthreads();
+            // ---- Assign (:196-216)
+            for (int p = tid; p < U; p += kEmdThreads) {
+                const int j = list[p], o = bid[j];
+                if (last || max_idx[o] == j) {
+                    const int prev = ainv[o];
+                    if (!last && prev != -1) asg[prev] = -1;
+                    ainv[o] = j;
+                    asg[j] = o;
+                    pts[o].w = __fadd_rn(pts[o].w, bid_inc[j]);
+                    max_inc[o] = -1e9f;
+                    max_idx[o] = INT_MAX;
+                }
+            }
+            __syncthreads();
+        }
+        __syncthreads();
+        // ---- CalcDist (:218-228)
+        for (int j = tid; j < n; j += kEmdThreads) {
+            const int k = asg[j];
+            const float dx = __fsub_rn(x1[3 * j], x2g[3 * k]), dy = __fsub_rn(x1[3 * j + 1], x2g[3 * k + 1]),
+                        dz = __fsub_rn(x1[3 * j + 2], x2g[3 * k + 2]);
+            A.dist[(size_t)b * n + j] = __fmaf_rn(dz, dz, __fmaf_rn(dx, dx, __fmul_rn(dy, dy)));
+            A.assignment[(size_t)b * n + j] = k;
+        }
+        if (A.iters_used && tid == 0) A.iters_used[b] = used;
+    }
+}
+
+// emd_cuda_backward (:270-305): only xyz1 receives a gradient; every point owns its row.
+__global__ void __launch_bounds__(256) emd_grad_kernel(const float *__restrict__ xyz1,
+                                                       const float *__restrict__ xyz2,
+                                                       const float *__restrict__ graddist,
+                                                       const int *__restrict__ assignment, long long total,
+                                                       int n, float *__restrict__ gradxyz1) {
+    for (long long e = blockIdx.x * 256LL + threadIdx.x; e < total; e += 256LL * gridDim.x) {
+        const long long b = e / n;
+        const float g = __fmul_rn(graddist[e], 2.f);
+        const float *p = xyz1 + 3 * e, *q = xyz2 + 3 * (b * n + assignment[e]);
+#pragma unroll
+        for (int c = 0; c < 3; ++c)
+            gradxyz1[3 * e + c] = __fadd_rn(gradxyz1[3 * e + c], __fmul_rn(g, __fsub_rn(p[c], q[c])));
+    }
+}
+
+}  // namespace houv
+
+using namespace houv;
+
+extern "C" size_t houv_emd_workspace_bytes(int B, int n) {
+    if (B <= 0 || n <= kEmdSmemN) return 0;
+    return sizeof(unsigned) * ((11 * (size_t)n + 3) & ~(size_t)3) * (size_t)B;
+}
+
+extern "C" int houv_emd_forward(const float *xyz1, const float *xyz2, int B, int n, float eps, int iters,
+                                float *dist, int *assignment, int *iters_used, void *workspace,
+                                size_t workspace_bytes, void *stream) {
+    if (B < 0 || n < 0 || iters <= 0 || !(eps >= 0.f)) return HOUV_E_BADARG;
+    if (B == 0 || n == 0) return 0;
+    if (!xyz1 || !xyz2 || !dist || !assignment) return HOUV_E_BADARG;
+    const size_t need = houv_emd_workspace_bytes(B, n);
+    if (need && (!workspace || workspace_bytes < need)) return HOUV_E_BADARG;
+    EmdArgs a;
+    a.xyz1 = xyz1; a.xyz2 = xyz2; a.dist = dist; a.assignment = assignment; a.iters_used = iters_used;
+    a.ws = (unsigned *)workspace; a.B = B; a.n = n; a.iters = iters; a.eps = eps;
+    const int grid = B < 148 * 4 ? B : 148 * 4;
+    if (n <= kEmdSmemN) {
+        static bool attr_set = false;
+        if (!attr_set) {
+            cudaError_t e = cudaFuncSetAttribute(emd_auction_kernel<true>,
+                                                 cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                 (int)(sizeof(unsigned) * 11 * kEmdSmemN));
+            if (e != cudaSuccess) return (int)e;
+            attr_set = true;
+        }
+        emd_auction_kernel<true><<<grid, kEmdThreads, sizeof(unsigned) * 11 * (size_t)n, (cudaStream_t)stream>>>(a);
+    } else {
+        emd_auction_kernel<false><<<grid, kEmdThreads, 0, (cudaStream_t)stream>>>(a);
+    }
+    return check_launch();
+}
+
+extern "C" int houv_emd_backward(const float *xyz1, const float *xyz2, const float *graddist,
+                                 const int *assignment, int B, int n, float *gradxyz1, void *stream) {
+    if (B < 0 || n < 0) return HOUV_E_BADARG;
+    if (B == 0 || n == 0) return 0;
+    if (!xyz1 || !xyz2 || !graddist || !assignment || !gradxyz1) return HOUV_E_BADARG;
+    const long long total = (long long)B * n;
+    long long blocks = (total + 255) / 256;
+    if (blocks > 148 * 32) blocks = 148 * 32;
+    emd_grad_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(xyz1, xyz2, graddist, assignment, total,
+                                                                       n, gradxyz1);
+    return check_launch();
+}

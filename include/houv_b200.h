@@ -21,6 +21,7 @@
  *   houv_cd_reduce           <- calc_cd / fscore reductions      registration/model_utils_completion.py:69-80
  *   houv_kabsch              <- SVDHead.forward     registration/model_utils.py:220-255
  *   houv_idam_step           <- IDAM refinement iteration tail     registration/models/idam.py:317-342
+ *   houv_emd_forward/backward <- emd.forward / emd.backward          utils/metrics/EMD/emd.cpp:14-29, emd_cuda.cu:230-316
  *   houv_icp                 <- o3d registration_icp call site    registration/train_ICP.py:148-151
  *   houv_pose_optimise       <- predict_model hot loop            registration/models/houv.py:106-138
  */
@@ -164,6 +165,22 @@ int houv_kabsch(const float *src, const float *src_corr, const float *weights, i
 int houv_idam_step(const float *src, const float *tgt, const void *corr_idx, int corr_is_int64,
                    const float *weight_logits, int B, int N, int M, float *src_out, float *R_acc,
                    float *t_acc, float *R_ab, float *t_ab, float *weights_out, void *stream);
+
+/* EMD approximation by the auction algorithm (K7; utils/metrics/EMD/emd_cuda.cu:230-268, emd_module.py:40-75):
+ *   xyz1[B,n,3] (prediction), xyz2[B,n,3] (ground truth), coordinates normalised to [0,1]; eps > 0 trades
+ *   accuracy for convergence, iters = iteration cap (the last one assigns every remaining point to its bid).
+ *   dist[B,n] = squared distance of xyz1[b,j] to xyz2[b,assignment[b,j]]; assignment[B,n] int32 (not
+ *   guaranteed to be a bijection, like the reference); iters_used[B] or NULL = iterations that still had
+ *   unassigned points.  All iterations run in one launch, one CTA per batch element.  Any n >= 1 and any B
+ *   (the reference needs n % 1024 == 0 and B <= 512); n > 4096 needs houv_emd_workspace_bytes(B,n) bytes of
+ *   device scratch.  Ties the reference leaves to thread scheduling are resolved towards the lowest index. */
+size_t houv_emd_workspace_bytes(int B, int n);
+int houv_emd_forward(const float *xyz1, const float *xyz2, int B, int n, float eps, int iters, float *dist,
+                     int *assignment, int *iters_used, void *workspace, size_t workspace_bytes, void *stream);
+/* gradxyz1[b,j] += 2*graddist[b,j]*(xyz1[b,j] - xyz2[b,assignment[b,j]]); xyz2 gets no gradient
+ * (emd_cuda.cu:270-305, emd_module.py:77-86). */
+int houv_emd_backward(const float *xyz1, const float *xyz2, const float *graddist, const int *assignment,
+                      int B, int n, float *gradxyz1, void *stream);
 
 /* Point-to-point ICP, one CTA per pair (train_ICP.py:148-151 call site; Open3D 0.9.0
  * algorithm restated, see csrc/icp.cu).

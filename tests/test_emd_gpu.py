@@ -1,0 +1,93 @@
+"""K7 (houv_emd_forward / houv_emd_backward) against the C restatement of the reference's auction
+(oracle/emd_oracle.c: bit-exact assignment and dist, the deterministic tie rules are shared) and against the
+reference's own CUDA extension built unmodified for sm_100a (oracle/_ref/emd.so: same EMD value; its result
+depends on thread scheduling where bids tie within 1e-6, so assignments are compared as a fraction)."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import emd as oe
+
+pytestmark = pytest.mark.gpu
+
+
+def _clouds(B, n, seed, quant=None):
+    rng = np.random.RandomState(seed)
+    x1 = rng.rand(B, n, 3).astype(np.float32)
+    x2 = rng.rand(B, n, 3).astype(np.float32)
+    if quant:  # coarse grid: exact value ties and duplicate points
+        x1 = (np.floor(x1 * quant) / quant).astype(np.float32)
+        x2 = (np.floor(x2 * quant) / quant).astype(np.float32)
+    return x1, x2
+
+
+@pytest.mark.parametrize("case", [
+    (2, 64, 0.005, 50, None), (3, 1024, 0.005, 50, None), (2, 2048, 0.002, 3000, None),
+    (1, 777, 0.004, 200, None), (2, 1, 0.005, 5, None), (1, 3, 0.005, 1, None),
+    (2, 512, 0.005, 300, 8), (1, 2048, 0.005, 50, 16), (1, 4096, 0.005, 20, None),
+    (2, 5000, 0.005, 12, None), (300, 128, 0.005, 100, None)])
+def test_forward_bit_exact_vs_oracle(case):
+    from houv_b200.emd import emd_forward
+    B, n, eps, iters, quant = case
+    x1, x2 = _clouds(B, n, n + iters, quant)
+    d, a, used = emd_forward(torch.from_numpy(x1).cuda(), torch.from_numpy(x2).cuda(), eps, iters, want_iters=True)
+    ed, ea, eu = oe.emd_forward(x1, x2, eps, iters)
+    assert np.array_equal(a.cpu().numpy(), ea)
+    assert np.array_equal(d.cpu().numpy(), ed)
+    assert np.array_equal(used.cpu().numpy(), eu)
+
+
+def test_converged_auction_is_a_bijection_near_the_optimum():
+    from scipy.optimize import linear_sum_assignment
+    from houv_b200.emd import emd_forward
+    x1, x2 = _clouds(4, 256, 5)
+    d, a, used = emd_forward(torch.from_numpy(x1).cuda(), torch.from_numpy(x2).cuda(), 0.001, 5000, want_iters=True)
+    a, d = a.cpu().numpy(), d.cpu().numpy()
+    for b in range(4):
+        if used[b] < 5000:  # converged before the forced last assignment
+            assert len(set(a[b])) == 256
+            C = np.sqrt(((x1[b][:, None] - x2[b][None]) ** 2).sum(-1))
+            r, c = linear_sum_assignment(C)
+            assert np.sqrt(d[b]).mean() <= C[r, c].mean() + 0.001 + 1e-6  # auction bound: n*eps over n points
+    assert (used.cpu().numpy() < 5000).any()
+
+
+@pytest.mark.skipif(not oe.ref_available(), reason="oracle/_ref/emd.so not built")
+@pytest.mark.parametrize("case", [(8, 1024, 0.005, 50), (4, 2048, 0.004, 1000)])
+def test_against_reference_extension(case):
+    from houv_b200.emd import emd_forward
+    B, n, eps, iters = case
+    x1, x2 = _clouds(B, n, 99)
+    t1, t2 = torch.from_numpy(x1).cuda(), torch.from_numpy(x2).cuda()
+    d, a = emd_forward(t1, t2, eps, iters)
+    rd, ra = oe.ref_emd_forward(t1, t2, eps, iters)
+    ours, ref = torch.sqrt(d).mean(1), torch.sqrt(rd).mean(1)
+    assert torch.allclose(ours, ref, rtol=0.02), (ours, ref)
+    assert float((a == ra).float().mean()) > 0.5
+
+
+def test_backward_and_autograd_vs_oracle():
+    from houv_b200.emd import emdModule, calc_emd
+    x1, x2 = _clouds(3, 512, 12)
+    t1 = torch.from_numpy(x1).cuda().requires_grad_()
+    t2 = torch.from_numpy(x2).cuda().requires_grad_()
+    dist, asg = emdModule()(t1, t2, 0.005, 50)
+    w = torch.rand_like(dist)
+    (dist * w).sum().backward()
+    eg = oe.emd_backward(x1, x2, w.cpu().numpy(), asg.cpu().numpy())
+    assert np.array_equal(t1.grad.cpu().numpy(), eg)
+    assert float(t2.grad.abs().max()) == 0.0  # emd_module.py:16 "we only calculate gradient for xyz1"
+    assert asg.dtype == torch.int32 and not asg.requires_grad
+    e = calc_emd(t1.detach(), t2.detach())
+    assert e.shape == (3,) and torch.allclose(e, torch.sqrt(dist.detach()).mean(1))
+
+
+def test_bad_inputs_raise():
+    from houv_b200.emd import emd_forward
+    a = torch.rand(2, 64, 3).cuda()
+    with pytest.raises(RuntimeError):
+        emd_forward(a, torch.rand(2, 32, 3).cuda(), 0.005, 50)
+    with pytest.raises(RuntimeError):
+        emd_forward(a, a, 0.005, 0)
+    with pytest.raises(RuntimeError):
+        emd_forward(a.cpu(), a, 0.005, 10)

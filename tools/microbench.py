@@ -284,6 +284,30 @@ def cmd_idam():
                           "torch_ops_same_gpu_ms": round(ref, 3), "ratio": round(ref / med, 1)}))
 
 
+def cmd_emd():
+    """K7 (houv_emd_forward) beside the reference's own EMD extension (oracle/_ref/emd.so, unmodified,
+    sm_100a) on the same GPU: training setting (eps 0.005, 50 iterations), evaluation setting
+    (pcn.py:169: eps 0.004, 3000 iterations) and emd_module.py:95-108 `test_emd` (20 x 8192, eps 0.05, 3000)."""
+    from houv_b200.emd import emd_forward
+    from oracle import emd as oe
+    for B, n, eps, iters in ((32, 2048, 0.005, 50), (32, 2048, 0.004, 3000), (148, 2048, 0.004, 3000),
+                             (20, 8192, 0.05, 3000)):
+        torch.manual_seed(0)
+        x1, x2 = torch.rand(B, n, 3).cuda(), torch.rand(B, n, 3).cuda()
+        med, _ = timeit(lambda: emd_forward(x1, x2, eps, iters), iters=3, warmup=1)
+        d, a, used = emd_forward(x1, x2, eps, iters, want_iters=True)
+        line = {"kernel": "K7 emd_forward", "B": B, "n": n, "eps": eps, "iters": iters, "ms": round(med, 3),
+                "emd": round(float(torch.sqrt(d).mean()), 6), "iters_used_max": int(used.max()),
+                "unique_frac": round(float(np.mean([len(set(r)) / n for r in a.cpu().numpy()])), 4)}
+        if oe.ref_available():
+            ref, _ = timeit(lambda: oe.ref_emd_forward(x1, x2, eps, iters), iters=2, warmup=1)
+            rd, ra = oe.ref_emd_forward(x1, x2, eps, iters)
+            line.update({"reference_ext_ms": round(ref, 2), "ratio": round(ref / med, 1),
+                         "reference_emd": round(float(torch.sqrt(rd).mean()), 6),
+                         "same_assignment_frac": round(float((ra == a).float().mean()), 4)})
+        print(json.dumps(line), flush=True)
+
+
 def cmd_pose():
     """K3 at the BASELINE shape: P pairs x 64 starts x `iters` iterations, 2048 points."""
     import numpy as np
@@ -321,4 +345,4 @@ def cmd_pose():
 
 
 if __name__ == "__main__":
-    {"probe": cmd_probe, "chamfer": cmd_chamfer, "pose": cmd_pose, "refext": cmd_refext, "icp": cmd_icp, "solve": cmd_solve, "refhouv": cmd_refhouv, "idam": cmd_idam}[sys.argv[1] if len(sys.argv) > 1 else "probe"]()
+    {"probe": cmd_probe, "chamfer": cmd_chamfer, "pose": cmd_pose, "refext": cmd_refext, "icp": cmd_icp, "solve": cmd_solve, "refhouv": cmd_refhouv, "idam": cmd_idam, "emd": cmd_emd}[sys.argv[1] if len(sys.argv) > 1 else "probe"]()
