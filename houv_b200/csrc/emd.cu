@@ -7,7 +7,7 @@
 // (registration/models/pcn.py:169), almost all of them with a handful of unassigned points, so the
 // reference's cost is launch latency x 7 x iters.  Here one CTA owns one batch element for the whole
 // auction: prices, bids, both assignment maps, the unassigned list and the target cloud (SoA) stay in
-// shared memory (44 B per point, n <= 4096; larger clouds use a caller-provided global workspace through
+// shared memory (48 B per point, n <= 4096; larger clouds use a caller-provided global workspace through
 // the same code, compiled a second time for generic addresses), phases are separated by __syncthreads() instead of launches, and the loop ends as
 // soon as nothing is unassigned (the reference's remaining iterations are no-ops).
 //
@@ -24,37 +24,58 @@
 namespace houv {
 
 constexpr int kEmdThreads = 1024;
-constexpr int kEmdSmemN = 4096;   // 44 B/point of state in shared memory up to here
+constexpr int kEmdSmall = 32;    // bidders resolved inside one warp
+constexpr int kEmdWords = 12;    // state words per point
+constexpr int kEmdSmemN = 4096;   // 48 B/point of state in shared memory up to here
 
 struct EmdArgs {
     const float *xyz1, *xyz2;
     float *dist;
     int *assignment;
     int *iters_used;   // [B] or null
-    unsigned *ws;      // global state, 11*n words per batch element, when n > kEmdSmemN
+    unsigned *ws;      // global state, 12*n words per batch element, when n > kEmdSmemN
     int B, n, iters;
     float eps;
 };
 
 struct Top2 {
     float best, better;
-    int i;
+    int i, i2;  // indices of best and of better (i2 is only a hint for the next sweep's bound)
 };
 
 // winner = larger value, lower index on equal values; better = max(winner's better, loser's best)
 __device__ __forceinline__ Top2 merge(const Top2 &a, const Top2 &b) {
     const bool b_wins = b.best > a.best || (b.best == a.best && (unsigned)b.i < (unsigned)a.i);
+    const Top2 &w = b_wins ? b : a, &l = b_wins ? a : b;
     Top2 r;
-    r.best = b_wins ? b.best : a.best;
-    r.i = b_wins ? b.i : a.i;
-    r.better = b_wins ? fmaxf(b.better, a.best) : fmaxf(a.better, b.best);
+    r.best = w.best;
+    r.i = w.i;
+    const bool from_loser = l.best > w.better;
+    r.better = from_loser ? l.best : w.better;
+    r.i2 = from_loser ? l.i : w.i2;
     return r;
 }
 
-// State of one batch element, 11 words per point: pts[n] = (x, y, z, price) of the target cloud and its
+__device__ __forceinline__ Top2 shfl_xor(const Top2 &t, int o) {
+    Top2 u;
+    u.best = __shfl_xor_sync(0xffffffffu, t.best, o);
+    u.better = __shfl_xor_sync(0xffffffffu, t.better, o);
+    u.i = __shfl_xor_sync(0xffffffffu, t.i, o);
+    u.i2 = __shfl_xor_sync(0xffffffffu, t.i2, o);
+    return u;
+}
+
+// The reference's value of candidate c = (x, y, z, price) for the bidder at (px, py, pz)   (:140-144)
+__device__ __forceinline__ float emd_value(const float4 c, float px, float py, float pz) {
+    const float dx = __fsub_rn(c.x, px), dy = __fsub_rn(c.y, py), dz = __fsub_rn(c.z, pz);
+    const float sq = __fmaf_rn(dz, dz, __fmaf_rn(dx, dx, __fmul_rn(dy, dy)));
+    return (float)((3.0 - (double)__fsqrt_rn(sq)) - (double)c.w);
+}
+
+// State of one batch element, 12 words per point: pts[n] = (x, y, z, price) of the target cloud and its
 // prices packed so that one 16-byte load feeds a candidate evaluation, then max_inc, bid_inc, max_idx,
-// ainv, asg, bid, list.  kSmem: the block lives in dynamic shared memory (pointers provably shared, so
-// LDS/STS/ATOMS); otherwise in the caller's workspace.
+// ainv, asg, bid, sec, list.  kSmem: the block lives in dynamic shared memory (pointers provably shared,
+// so LDS/STS/ATOMS); otherwise in the caller's workspace.
 template <bool kSmem>
 __global__ void __launch_bounds__(kEmdThreads, 1) emd_auction_kernel(const EmdArgs A) {
     extern __shared__ __align__(16) unsigned sm_u[];
@@ -62,30 +83,34 @@ __global__ void __launch_bounds__(kEmdThreads, 1) emd_auction_kernel(const EmdAr
     __shared__ Top2 s_merge[kEmdThreads / 32];
     const int n = A.n, tid = threadIdx.x;
     for (int b = blockIdx.x; b < A.B; b += gridDim.x) {
-        unsigned *base = kSmem ? sm_u : A.ws + (size_t)b * ((11 * (size_t)n + 3) & ~(size_t)3);  // 16-byte aligned
+        unsigned *base = kSmem ? sm_u : A.ws + (size_t)b * kEmdWords * n;  // 16-byte aligned (12 words)
         float4 *pts = reinterpret_cast<float4 *>(base);
         float *max_inc = reinterpret_cast<float *>(base + 4 * (size_t)n);
         float *bid_inc = max_inc + n;
         int *max_idx = reinterpret_cast<int *>(bid_inc + n);
         int *ainv = max_idx + n;
         int *asg = ainv + n;
-        int *bid = asg + n;
-        int *list = bid + n;
+        int *bid = asg + n;   // last best object of a point (its bid)
+        int *sec = bid + n;   // last second-best object of a point
+        int *list = sec + n;
         const float *x1 = A.xyz1 + (size_t)b * n * 3;
         const float *x2g = A.xyz2 + (size_t)b * n * 3;
         __syncthreads();
         for (int k = tid; k < n; k += kEmdThreads) {
             pts[k] = make_float4(x2g[3 * k], x2g[3 * k + 1], x2g[3 * k + 2], 0.f);
-            max_inc[k] = 0.f; max_idx[k] = INT_MAX; ainv[k] = -1; asg[k] = -1;
+            max_inc[k] = 0.f; max_idx[k] = INT_MAX; ainv[k] = -1; asg[k] = -1; bid[k] = -1; sec[k] = -1;
         }
         int used = 0;
+        bool have_list = false;  // the small path below leaves the next iteration's list behind
         for (int it = 0; it < A.iters; ++it) {
             const bool last = it == A.iters - 1;
-            if (tid == 0) s_cnt = 0;
-            __syncthreads();
-            for (int j = tid; j < n; j += kEmdThreads)
-                if (asg[j] == -1) list[atomicAdd(&s_cnt, 1)] = j;
-            __syncthreads();
+            if (!have_list) {
+                if (tid == 0) s_cnt = 0;
+                __syncthreads();
+                for (int j = tid; j < n; j += kEmdThreads)
+                    if (asg[j] == -1) list[atomicAdd(&s_cnt, 1)] = j;
+                __syncthreads();
+            }
             const int U = s_cnt;
             if (U == 0) break;
             ++used;
@@ -94,46 +119,41 @@ __global__ void __launch_bounds__(kEmdThreads, 1) emd_auction_kernel(const EmdAr
             while (G * 2 * U <= kEmdThreads) G *= 2;
             const int groups = kEmdThreads / G;
             const int lane_g = tid & (G - 1);
+            const int w = G < 32 ? G : 32;  // lanes of a warp that serve the same bidder
             for (int p0 = 0; p0 < U; p0 += groups) {
                 const int p = p0 + tid / G;
                 const bool valid = p < U;
                 const int j = valid ? list[p] : 0;
-                Top2 t{-1e9f, -1e9f, -1};
+                Top2 t{-1e9f, -1e9f, -1, -1};
                 float px = 0.f, py = 0.f, pz = 0.f;
-                const int w = G < 32 ? G : 32;  // lanes of this warp that serve the same bidder
-                // First candidate of every lane, exactly; the second best of those w values is a lower bound
-                // of the bidder's final second best and becomes the lanes' common pruning threshold (a lane
-                // that only sees n/G candidates would otherwise never build a useful one of its own).
+                float bound = -1e9f;  // a lower bound of the bidder's final second best; -1e9 keeps everything
+                // Two cheap lower bounds before the sweep.  (1) The bidder's best and second-best objects
+                // of its previous bid, at today's prices: few prices moved since, so the smaller of the two
+                // values is usually within a few eps of the final second best.  (2) The first candidate of
+                // every lane, exactly; the second best of those w values.  Without them a lane that sees
+                // only n/G candidates never builds a useful bound of its own.
                 if (valid) {
                     px = __ldg(x1 + 3 * j); py = __ldg(x1 + 3 * j + 1); pz = __ldg(x1 + 3 * j + 2);
+                    const int o1 = bid[j], o2 = sec[j];
+                    if (o1 >= 0 && o2 >= 0)
+                        bound = fminf(emd_value(pts[o1], px, py, pz), emd_value(pts[o2], px, py, pz));
                     if (lane_g < n) {
-                        const float4 c = pts[lane_g];
-                        const float dx = __fsub_rn(c.x, px), dy = __fsub_rn(c.y, py), dz = __fsub_rn(c.z, pz);
-                        const float sq = __fmaf_rn(dz, dz, __fmaf_rn(dx, dx, __fmul_rn(dy, dy)));
-                        t.best = (float)((3.0 - (double)__fsqrt_rn(sq)) - (double)c.w);
+                        t.best = emd_value(pts[lane_g], px, py, pz);
                         t.i = lane_g;
                     }
                 }
-                float shared_better = -1e9f;
                 if (w > 1) {
                     Top2 g = t;
-                    for (int o = w >> 1; o > 0; o >>= 1) {
-                        Top2 u;
-                        u.best = __shfl_xor_sync(0xffffffffu, g.best, o);
-                        u.better = __shfl_xor_sync(0xffffffffu, g.better, o);
-                        u.i = __shfl_xor_sync(0xffffffffu, g.i, o);
-                        g = merge(g, u);
-                    }
-                    shared_better = g.better;
+                    for (int o = w >> 1; o > 0; o >>= 1) g = merge(g, shfl_xor(g, o));
+                    bound = fmaxf(bound, g.better);
                 }
                 if (valid) {
                     // A candidate whose value is certainly below a lower bound of the bidder's final second
-                    // best (this lane's running one, or the common one above) cannot be among its two best,
-                    // so it is dropped on the squared distance alone: value < bound  <=>  sqrt(sq) > 3 - bound
-                    // - price, tested with a margin 16x the rounding of the quantities involved.  That keeps
-                    // the square root, the two float->double conversions, the double subtractions and the
-                    // conversion back (XU / FP64 pipes) off all but the few candidates that can matter.
-                    float bound = shared_better;  // -1e9 keeps everything
+                    // best cannot be among its two best, so it is dropped on the squared distance alone:
+                    // value < bound  <=>  sqrt(sq) > 3 - bound - price, tested with a margin 16x the rounding
+                    // of the quantities involved.  That keeps the square root, the two float->double
+                    // conversions, the double subtractions and the conversion back (XU / FP64 pipes) off all
+                    // but the few candidates that can matter.
                     float fa = 3.f - bound;
                     float fb = fa + 0x1p-20f * (fabsf(fa) + fabsf(bound) + 4.f);
 #pragma unroll 2
@@ -144,8 +164,8 @@ __global__ void __launch_bounds__(kEmdThreads, 1) emd_auction_kernel(const EmdAr
                         const float th = fmaf(c.w, -(1.f - 0x1p-20f), fb);  // 3 - bound - price + margin
                         if (th <= 0.f || sq > th * th) continue;
                         const float d = (float)((3.0 - (double)__fsqrt_rn(sq)) - (double)c.w);
-                        if (d > t.best) { t.better = t.best; t.best = d; t.i = k; }
-                        else if (d > t.better) t.better = d;
+                        if (d > t.best) { t.better = t.best; t.i2 = t.i; t.best = d; t.i = k; }
+                        else if (d > t.better) { t.better = d; t.i2 = k; }
                         else continue;
                         if (t.better > bound) {
                             bound = t.better;
@@ -154,25 +174,16 @@ __global__ void __launch_bounds__(kEmdThreads, 1) emd_auction_kernel(const EmdAr
                         }
                     }
                 }
-                for (int o = w >> 1; o > 0; o >>= 1) {
-                    Top2 u;
-                    u.best = __shfl_xor_sync(0xffffffffu, t.best, o);
-                    u.better = __shfl_xor_sync(0xffffffffu, t.better, o);
-                    u.i = __shfl_xor_sync(0xffffffffu, t.i, o);
-                    t = merge(t, u);
-                }
-                if (G > 32) {  // uniform across the CTA: G depends on U only
-                    if ((tid & 31) == 0) s_merge[tid >> 5] = t;
-                    __syncthreads();
-                    if (lane_g == 0) {
-                        const int w0 = tid >> 5;
-                        for (int q = 1; q < G / 32; ++q) t = merge(t, s_merge[w0 + q]);
-                    }
-                    __syncthreads();
-                }
-                if (valid && lane_g == 0) {
+                for (int o = w >> 1; o > 0; o >>= 1) t = merge(t, shfl_xor(t, o));
+                if (U <= kEmdSmall) {
+                    // at most 32 bidders: one sweep round; hand the per-warp (G > 32) or per-bidder results
+                    // to warp 0 through shared memory
+                    if (G > 32) { if ((tid & 31) == 0) s_merge[tid >> 5] = t; }
+                    else if (valid && lane_g == 0) s_merge[p] = t;
+                } else if (valid && lane_g == 0) {
                     const float inc = __fadd_rn(__fsub_rn(t.best, t.better), A.eps);
                     bid[j] = t.i;
+                    sec[j] = t.i2;
                     bid_inc[j] = inc;
                     // float max through the signed-int order: increments are >= 0, the cleared
                     // value -1e9 is negative (emd_cuda.cu:10-20 is the same max)
@@ -180,6 +191,62 @@ __global__ void __launch_bounds__(kEmdThreads, 1) emd_auction_kernel(const EmdAr
                 }
             }
             __syncthreads();
+            if (U <= kEmdSmall) {
+                // ---- GetMax + Assign for <= 32 bidders inside warp 0, lane = bidder: no scratch arrays, no
+                // block barriers between the phases, and the next iteration's unassigned list (losers and
+                // displaced owners) is written directly instead of rescanning all n points.
+                if (tid < 32) {
+                    const int lane = tid;
+                    Top2 t = s_merge[lane];
+                    if (G > 32) {
+                        const int wb = G >> 5;  // warps (= lanes here) per bidder, a power of two
+                        for (int o = wb >> 1; o > 0; o >>= 1) t = merge(t, shfl_xor(t, o));
+                        const int src = (lane * wb) & 31;
+                        t.best = __shfl_sync(0xffffffffu, t.best, src);
+                        t.better = __shfl_sync(0xffffffffu, t.better, src);
+                        t.i = __shfl_sync(0xffffffffu, t.i, src);
+                        t.i2 = __shfl_sync(0xffffffffu, t.i2, src);
+                    }
+                    const bool bidder = lane < U;
+                    const int j = bidder ? list[lane] : -1;
+                    const int o = bidder ? t.i : -1 - lane;  // distinct dummies never match
+                    const float inc = __fadd_rn(__fsub_rn(t.best, t.better), A.eps);
+                    float mx = inc;
+                    for (int q = 0; q < U; ++q) {
+                        const int oq = __shfl_sync(0xffffffffu, o, q);
+                        const float iq = __shfl_sync(0xffffffffu, inc, q);
+                        if (oq == o && iq > mx) mx = iq;
+                    }
+                    const bool qual = (double)inc - 1e-6 <= (double)mx && (double)mx <= (double)inc + 1e-6;
+                    bool win = qual;
+                    for (int q = 0; q < U; ++q) {
+                        const int oq = __shfl_sync(0xffffffffu, o, q);
+                        const int jq = __shfl_sync(0xffffffffu, j, q);
+                        const bool qq = __shfl_sync(0xffffffffu, (int)qual, q) != 0;
+                        if (oq == o && qq && jq < j) win = false;
+                    }
+                    win = bidder && (win || last);
+                    int item = -1;  // this lane's contribution to the next list
+                    if (bidder) { bid[j] = t.i; sec[j] = t.i2; }
+                    if (win) {
+                        const int prev = ainv[o];
+                        if (!last && prev != -1) { asg[prev] = -1; item = prev; }
+                        ainv[o] = j;
+                        asg[j] = o;
+                        pts[o].w = __fadd_rn(pts[o].w, inc);
+                    } else if (bidder) {
+                        item = j;
+                    }
+                    const unsigned has = __ballot_sync(0xffffffffu, item != -1);
+                    __syncwarp();  // every lane has read list[] before it is overwritten
+                    if (item != -1) list[__popc(has & ((1u << lane) - 1))] = item;
+                    if (lane == 0) s_cnt = __popc(has);
+                }
+                have_list = true;
+                __syncthreads();
+                continue;
+            }
+            have_list = false;
             // ---- GetMax (:181-194): lowest j among the bidders within 1e-6 of the object's maximum
             for (int p = tid; p < U; p += kEmdThreads) {
                 const int j = list[p], o = bid[j];
@@ -237,7 +304,7 @@ using namespace houv;
 
 extern "C" size_t houv_emd_workspace_bytes(int B, int n) {
     if (B <= 0 || n <= kEmdSmemN) return 0;
-    return sizeof(unsigned) * ((11 * (size_t)n + 3) & ~(size_t)3) * (size_t)B;
+    return sizeof(unsigned) * kEmdWords * (size_t)n * (size_t)B;
 }
 
 extern "C" int houv_emd_forward(const float *xyz1, const float *xyz2, int B, int n, float eps, int iters,
@@ -257,11 +324,11 @@ extern "C" int houv_emd_forward(const float *xyz1, const float *xyz2, int B, int
         if (!attr_set) {
             cudaError_t e = cudaFuncSetAttribute(emd_auction_kernel<true>,
                                                  cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                                 (int)(sizeof(unsigned) * 11 * kEmdSmemN));
+                                                 (int)(sizeof(unsigned) * kEmdWords * kEmdSmemN));
             if (e != cudaSuccess) return (int)e;
             attr_set = true;
         }
-        emd_auction_kernel<true><<<grid, kEmdThreads, sizeof(unsigned) * 11 * (size_t)n, (cudaStream_t)stream>>>(a);
+        emd_auction_kernel<true><<<grid, kEmdThreads, sizeof(unsigned) * kEmdWords * (size_t)n, (cudaStream_t)stream>>>(a);
     } else {
         emd_auction_kernel<false><<<grid, kEmdThreads, 0, (cudaStream_t)stream>>>(a);
     }
