@@ -226,14 +226,16 @@ extern "C" int houv_nn_search(const float *query, const float *target, int B, in
 static bool want_symmetric(int B, int nr, long long ctas) {
     if (g_nn_variant == 10) return true;
     if (g_nn_variant >= 0) return false;
-    return nr >= 1024 && ctas >= 148;
+    return nr >= 1024 && ctas >= 100;  // ctas counts the column splits of small batches
 }
 
 extern "C" size_t houv_chamfer3d_workspace_bytes(int B, int N, int M) {
     if (B <= 0 || N <= 0 || M <= 0) return 0;
     const int nr = N >= M ? N : M, nc = N >= M ? M : N;
-    if (nr <= kSymChunkRows) return 0;
-    return sizeof(unsigned long long) * (size_t)B * (size_t)nc;
+    // column keys when the rows span several CTAs, row keys when the columns are split
+    const size_t n_c = nr > kSymChunkRows ? (size_t)B * (size_t)nc : 0;
+    const size_t n_r = sym_col_splits(B, nr, nc) > 1 ? (size_t)B * (size_t)nr : 0;
+    return sizeof(unsigned long long) * (n_c + n_r);
 }
 
 extern "C" int houv_chamfer3d_forward_ws(const float *xyz1, const float *xyz2, int B, int N, int M,
@@ -253,13 +255,16 @@ extern "C" int houv_chamfer3d_forward_ws(const float *xyz1, const float *xyz2, i
     const size_t need = houv_chamfer3d_workspace_bytes(B, N, M);
     const bool ws_ok = need == 0 || (workspace && workspace_bytes >= need &&
                                      (reinterpret_cast<uintptr_t>(workspace) & 7) == 0);
-    if (ws_ok && want_symmetric(B, nr, chunks * B)) {
+    const int splits = sym_col_splits(B, nr, nc);
+    if (ws_ok && want_symmetric(B, nr, chunks * B * splits)) {
         SymArgs s;
         s.rows = one_rows ? xyz1 : xyz2; s.cols = one_rows ? xyz2 : xyz1;
         s.dist_r = one_rows ? dist1 : dist2; s.idx_r = one_rows ? idx1 : idx2;
         s.dist_c = one_rows ? dist2 : dist1; s.idx_c = one_rows ? idx2 : idx1;
-        s.keys = need ? static_cast<unsigned long long *>(workspace) : nullptr;
-        s.B = B; s.nr = nr; s.nc = nc;
+        unsigned long long *ws = static_cast<unsigned long long *>(workspace);
+        s.keys = chunks > 1 ? ws : nullptr;
+        s.row_keys = splits > 1 ? ws + (chunks > 1 ? (size_t)B * nc : 0) : nullptr;
+        s.B = B; s.nr = nr; s.nc = nc; s.cols_per_split = nc;
         return launch_chamfer_sym(s, (cudaStream_t)stream);
     }
     NNArgs a;

@@ -21,9 +21,14 @@
 //    their minimum from a per-superblock reduction; the candidate equal to the known minimum
 //    with the smallest index is the reference's first minimum (chamfer3D.cu:36,46,126);
 //  * with more than one row chunk the column results of the chunks are combined with a 64-bit
-//    atomicMin on (distance bits << 32 | index) keys in a caller-provided workspace.
+//    atomicMin on (distance bits << 32 | index) keys in a caller-provided workspace;
+//  * small batches (fewer CTAs than SMs) are also split along the columns (gridDim.z): each CTA sweeps
+//    its rows against a slice of the columns and the row results are combined through the same kind
+//    of keys (smallest distance, then smallest index = the reference's first minimum).
 // Cost per evaluation: 6 FMA-pipe + 2 ALU-pipe lane-cycles for BOTH directions, against
 // 2 x (6 + 1) in the two-scan kernel (chamfer_fwd.cu).
+#include <stdlib.h>
+
 #include "common.cuh"
 
 namespace houv {
@@ -115,6 +120,9 @@ __global__ void __launch_bounds__(kSThreads, 2) chamfer_sym_kernel(const SymArgs
     const int row0 = 8 * t;
     const int rbase = blockIdx.x * kSRows;
     const int nr = A.nr, nc = A.nc;
+    const int c_lo = blockIdx.z * A.cols_per_split;          // this CTA's slice of the columns
+    const int c_hi = min(nc, c_lo + A.cols_per_split);
+    if (c_lo >= nc) return;
     const int nrows = min(kSRows, nr - rbase);  // real rows of this chunk (> 0 by grid size)
     const bool scan_active = 256 * w < nrows;   // warp-uniform
     const int nsg = (nrows + kSGrp - 1) / kSGrp;
@@ -147,8 +155,8 @@ __global__ void __launch_bounds__(kSThreads, 2) chamfer_sym_kernel(const SymArgs
             best[r] = inf; prev[r] = inf; gid[r] = 0; idxr[r] = 0;
         }
 
-        for (int t0 = 0; t0 < nc; t0 += kSTile) {
-            const int cnt = min(kSTile, nc - t0);
+        for (int t0 = c_lo; t0 < c_hi; t0 += kSTile) {
+            const int cnt = min(kSTile, c_hi - t0);
             const int cnt_pad = (cnt + kSGrp - 1) / kSGrp * kSGrp;
             const int nsb = cnt_pad / kSGrp;
             const int sb0 = t0 / kSGrp;  // global number of this tile's first superblock
@@ -288,24 +296,46 @@ __global__ void __launch_bounds__(kSThreads, 2) chamfer_sym_kernel(const SymArgs
         for (int r = 0; r < 8; ++r) {
             const int i = row0 + r;
             if (i < nrows) {
-                A.dist_r[(size_t)b * nr + rbase + i] = best[r];
-                A.idx_r[(size_t)b * nr + rbase + i] = idxr[r];
+                const size_t o = (size_t)b * nr + rbase + i;
+                if (A.row_keys) {
+                    atomicMin(A.row_keys + o, ((unsigned long long)__float_as_uint(best[r]) << 32) |
+                                                  (unsigned)idxr[r]);
+                } else {
+                    A.dist_r[o] = best[r];
+                    A.idx_r[o] = idxr[r];
+                }
             }
         }
     }
 }
 
-__global__ void chamfer_sym_unpack(const unsigned long long *keys, float *dist, int *idx, size_t n) {
-    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) {
-        const unsigned long long k = keys[i];
-        dist[i] = __uint_as_float((unsigned)(k >> 32));
-        idx[i] = (int)(unsigned)(k & 0xffffffffull);
+__global__ void chamfer_sym_unpack(const unsigned long long *keys, float *dist, int *idx, size_t n,
+                                   const unsigned long long *keys2, float *dist2, int *idx2, size_t n2) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) {  // second segment
+        i -= n;
+        if (i >= n2) return;
+        keys = keys2; dist = dist2; idx = idx2;
     }
+    const unsigned long long k = keys[i];
+    dist[i] = __uint_as_float((unsigned)(k >> 32));
+    idx[i] = (int)(unsigned)(k & 0xffffffffull);
 }
 
-// Launch the symmetric forward with `rows` = the cloud chunked over CTAs.  keys: workspace of
-// B*nc 64-bit words, required when nr > kSRows.
+int sym_col_splits(int B, int nr, int nc) {
+    static const int forced = getenv("HOUV_K1S_SPLIT") ? atoi(getenv("HOUV_K1S_SPLIT")) : 0;
+    const long long ctas = (long long)((nr + kSRows - 1) / kSRows) * B;
+    // one CTA per SM: slices narrower than that pay the per-CTA row recovery too often (measured, C2:
+    // 4 slices 68.6 us, 8 slices 72.7 us, directed kernel 74.7 us)
+    int s = forced > 0 ? forced : (ctas >= 148 ? 1 : (int)(148 / ctas));
+    const int most = nc / 256;  // at least 256 columns per slice
+    if (s > most) s = most;
+    return s < 1 ? 1 : s;
+}
+
+// Launch the symmetric forward with `rows` = the cloud chunked over CTAs.  a.keys: workspace of
+// B*nc 64-bit words, required when nr > kSRows; a.row_keys: B*nr words, required when
+// sym_col_splits() > 1.
 int launch_chamfer_sym(const SymArgs &a, cudaStream_t st) {
     static bool attr_set = false;
     if (!attr_set) {
@@ -316,19 +346,23 @@ int launch_chamfer_sym(const SymArgs &a, cudaStream_t st) {
         attr_set = true;
     }
     const int chunks = (a.nr + kSRows - 1) / kSRows;
-    if (chunks > 1) {
-        if (!a.keys) return HOUV_E_BADARG;
-        cudaError_t e = cudaMemsetAsync(a.keys, 0xff, sizeof(unsigned long long) * (size_t)a.B * a.nc, st);
-        if (e != cudaSuccess) return (int)e;
-    }
+    const int splits = sym_col_splits(a.B, a.nr, a.nc);
     SymArgs k = a;
     if (chunks == 1) k.keys = nullptr;
-    dim3 grid(chunks, a.B < 65535 ? a.B : 65535);
+    if (splits == 1) k.row_keys = nullptr;
+    if ((chunks > 1 && !k.keys) || (splits > 1 && !k.row_keys)) return HOUV_E_BADARG;
+    k.cols_per_split = splits == 1 ? a.nc : ((a.nc + splits - 1) / splits + kSGrp - 1) / kSGrp * kSGrp;
+    const size_t n_c = chunks > 1 ? (size_t)a.B * a.nc : 0, n_r = splits > 1 ? (size_t)a.B * a.nr : 0;
+    cudaError_t e = cudaSuccess;
+    if (n_c) e = cudaMemsetAsync(k.keys, 0xff, sizeof(unsigned long long) * n_c, st);
+    if (e == cudaSuccess && n_r) e = cudaMemsetAsync(k.row_keys, 0xff, sizeof(unsigned long long) * n_r, st);
+    if (e != cudaSuccess) return (int)e;
+    dim3 grid(chunks, a.B < 65535 ? a.B : 65535, splits);
     chamfer_sym_kernel<8><<<grid, kSThreads, sizeof(SmemK1s), st>>>(k);
-    if (int e = check_launch()) return e;
-    if (chunks > 1) {
-        const size_t n = (size_t)a.B * a.nc;
-        chamfer_sym_unpack<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(a.keys, a.dist_c, a.idx_c, n);
+    if (int err = check_launch()) return err;
+    if (n_c + n_r) {
+        chamfer_sym_unpack<<<(unsigned)((n_c + n_r + 255) / 256), 256, 0, st>>>(
+            k.keys, a.dist_c, a.idx_c, n_c, k.row_keys, a.dist_r, a.idx_r, n_r);
         return check_launch();
     }
     return 0;

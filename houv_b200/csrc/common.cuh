@@ -46,11 +46,16 @@ struct SymArgs {
     float *dist_c;       // [B,nc]
     int *idx_c;          // [B,nc]  index into rows
     unsigned long long *keys;  // [B,nc] workspace when gridDim.x > 1, else null
+    unsigned long long *row_keys;  // [B,nr] workspace when the columns are split over gridDim.z > 1
     int B, nr, nc;
+    int cols_per_split;  // multiple of 64; nc when there is one split
 };
 
 constexpr int kSymChunkRows = 2048;  // rows of `rows` handled by one CTA
 int launch_chamfer_sym(const SymArgs &a, cudaStream_t st);
+// Column splits the symmetric kernel uses for this shape (1 = none): small batches are cut along the
+// columns as well so that the grid covers the GPU.  Shared by the launcher and the workspace size.
+int sym_col_splits(int B, int nr, int nc);
 
 inline int check_launch() {
     cudaError_t e = cudaGetLastError();
