@@ -17,7 +17,9 @@
 //   dist = fma(dz,dz,fma(dx,dx,dy*dy)) (:222-226)
 // The two places where the reference's result depends on scheduling are fixed the same way as in
 // oracle/emd_oracle.c: equal values -> lowest k; bidders within 1e-6 of an object's maximum -> lowest j.
+#include <cooperative_groups.h>
 #include <limits.h>
+#include <stdlib.h>
 
 #include "common.cuh"
 
@@ -72,6 +74,64 @@ __device__ __forceinline__ float emd_value(const float4 c, float px, float py, f
     return (float)((3.0 - (double)__fsqrt_rn(sq)) - (double)c.w);
 }
 
+// One bidder's sweep over the candidates k = lane_g, lane_g + G, ... of pts[0..n): the exact two best values
+// (reference arithmetic and tie rule) merged over the w = min(G, 32) lanes of the warp that serve it.
+// o1, o2 = the bidder's best and second-best objects of its previous bid (-1: none).  Warp-convergent.
+__device__ __forceinline__ Top2 sweep_bidder(bool valid, int j, int o1, int o2, const float *x1,
+                                             const float4 *pts, int n, int lane_g, int G, int w) {
+    Top2 t{-1e9f, -1e9f, -1, -1};
+    float px = 0.f, py = 0.f, pz = 0.f;
+    float bound = -1e9f;  // a lower bound of the bidder's final second best; -1e9 keeps everything
+    // Two cheap lower bounds before the sweep.  (1) The bidder's best and second-best objects
+    // of its previous bid, at today's prices: few prices moved since, so the smaller of the two
+    // values is usually within a few eps of the final second best.  (2) The first candidate of
+    // every lane, exactly; the second best of those w values.  Without them a lane that sees
+    // only n/G candidates never builds a useful bound of its own.
+    if (valid) {
+        px = __ldg(x1 + 3 * j); py = __ldg(x1 + 3 * j + 1); pz = __ldg(x1 + 3 * j + 2);
+        if (o1 >= 0 && o2 >= 0)
+            bound = fminf(emd_value(pts[o1], px, py, pz), emd_value(pts[o2], px, py, pz));
+        if (lane_g < n) {
+            t.best = emd_value(pts[lane_g], px, py, pz);
+            t.i = lane_g;
+        }
+    }
+    if (w > 1) {
+        Top2 g = t;
+        for (int o = w >> 1; o > 0; o >>= 1) g = merge(g, shfl_xor(g, o));
+        bound = fmaxf(bound, g.better);
+    }
+    if (valid) {
+        // A candidate whose value is certainly below a lower bound of the bidder's final second
+        // best cannot be among its two best, so it is dropped on the squared distance alone:
+        // value < bound  <=>  sqrt(sq) > 3 - bound - price, tested with a margin 16x the rounding
+        // of the quantities involved.  That keeps the square root, the two float->double
+        // conversions, the double subtractions and the conversion back (XU / FP64 pipes) off all
+        // but the few candidates that can matter.
+        float fa = 3.f - bound;
+        float fb = fa + 0x1p-20f * (fabsf(fa) + fabsf(bound) + 4.f);
+#pragma unroll 2
+        for (int k = lane_g + G; k < n; k += G) {
+            const float4 c = pts[k];
+            const float dx = __fsub_rn(c.x, px), dy = __fsub_rn(c.y, py), dz = __fsub_rn(c.z, pz);
+            const float sq = __fmaf_rn(dz, dz, __fmaf_rn(dx, dx, __fmul_rn(dy, dy)));
+            const float th = fmaf(c.w, -(1.f - 0x1p-20f), fb);  // 3 - bound - price + margin
+            if (th <= 0.f || sq > th * th) continue;
+            const float d = (float)((3.0 - (double)__fsqrt_rn(sq)) - (double)c.w);
+            if (d > t.best) { t.better = t.best; t.i2 = t.i; t.best = d; t.i = k; }
+            else if (d > t.better) { t.better = d; t.i2 = k; }
+            else continue;
+            if (t.better > bound) {
+                bound = t.better;
+                fa = 3.f - bound;
+                fb = fa + 0x1p-20f * (fabsf(fa) + fabsf(bound) + 4.f);
+            }
+        }
+    }
+    for (int o = w >> 1; o > 0; o >>= 1) t = merge(t, shfl_xor(t, o));
+    return t;
+}
+
 // State of one batch element, 12 words per point: pts[n] = (x, y, z, price) of the target cloud and its
 // prices packed so that one 16-byte load feeds a candidate evaluation, then max_inc, bid_inc, max_idx,
 // ainv, asg, bid, sec, list.  kSmem: the block lives in dynamic shared memory (pointers provably shared,
@@ -124,57 +184,7 @@ __global__ void __launch_bounds__(kEmdThreads, 1) emd_auction_kernel(const EmdAr
                 const int p = p0 + tid / G;
                 const bool valid = p < U;
                 const int j = valid ? list[p] : 0;
-                Top2 t{-1e9f, -1e9f, -1, -1};
-                float px = 0.f, py = 0.f, pz = 0.f;
-                float bound = -1e9f;  // a lower bound of the bidder's final second best; -1e9 keeps everything
-                // Two cheap lower bounds before the sweep.  (1) The bidder's best and second-best objects
-                // of its previous bid, at today's prices: few prices moved since, so the smaller of the two
-                // values is usually within a few eps of the final second best.  (2) The first candidate of
-                // every lane, exactly; the second best of those w values.  Without them a lane that sees
-                // only n/G candidates never builds a useful bound of its own.
-                if (valid) {
-                    px = __ldg(x1 + 3 * j); py = __ldg(x1 + 3 * j + 1); pz = __ldg(x1 + 3 * j + 2);
-                    const int o1 = bid[j], o2 = sec[j];
-                    if (o1 >= 0 && o2 >= 0)
-                        bound = fminf(emd_value(pts[o1], px, py, pz), emd_value(pts[o2], px, py, pz));
-                    if (lane_g < n) {
-                        t.best = emd_value(pts[lane_g], px, py, pz);
-                        t.i = lane_g;
-                    }
-                }
-                if (w > 1) {
-                    Top2 g = t;
-                    for (int o = w >> 1; o > 0; o >>= 1) g = merge(g, shfl_xor(g, o));
-                    bound = fmaxf(bound, g.better);
-                }
-                if (valid) {
-                    // A candidate whose value is certainly below a lower bound of the bidder's final second
-                    // best cannot be among its two best, so it is dropped on the squared distance alone:
-                    // value < bound  <=>  sqrt(sq) > 3 - bound - price, tested with a margin 16x the rounding
-                    // of the quantities involved.  That keeps the square root, the two float->double
-                    // conversions, the double subtractions and the conversion back (XU / FP64 pipes) off all
-                    // but the few candidates that can matter.
-                    float fa = 3.f - bound;
-                    float fb = fa + 0x1p-20f * (fabsf(fa) + fabsf(bound) + 4.f);
-#pragma unroll 2
-                    for (int k = lane_g + G; k < n; k += G) {
-                        const float4 c = pts[k];
-                        const float dx = __fsub_rn(c.x, px), dy = __fsub_rn(c.y, py), dz = __fsub_rn(c.z, pz);
-                        const float sq = __fmaf_rn(dz, dz, __fmaf_rn(dx, dx, __fmul_rn(dy, dy)));
-                        const float th = fmaf(c.w, -(1.f - 0x1p-20f), fb);  // 3 - bound - price + margin
-                        if (th <= 0.f || sq > th * th) continue;
-                        const float d = (float)((3.0 - (double)__fsqrt_rn(sq)) - (double)c.w);
-                        if (d > t.best) { t.better = t.best; t.i2 = t.i; t.best = d; t.i = k; }
-                        else if (d > t.better) { t.better = d; t.i2 = k; }
-                        else continue;
-                        if (t.better > bound) {
-                            bound = t.better;
-                            fa = 3.f - bound;
-                            fb = fa + 0x1p-20f * (fabsf(fa) + fabsf(bound) + 4.f);
-                        }
-                    }
-                }
-                for (int o = w >> 1; o > 0; o >>= 1) t = merge(t, shfl_xor(t, o));
+                const Top2 t = sweep_bidder(valid, j, valid ? bid[j] : -1, valid ? sec[j] : -1, x1, pts, n, lane_g, G, w);
                 if (U <= kEmdSmall) {
                     // at most 32 bidders: one sweep round; hand the per-warp (G > 32) or per-bidder results
                     // to warp 0 through shared memory
@@ -282,6 +292,181 @@ __global__ void __launch_bounds__(kEmdThreads, 1) emd_auction_kernel(const EmdAr
     }
 }
 
+// The same auction with kC CTAs (a thread-block cluster) per batch element, for batches too small to give
+// every SM an element of its own.  The bidders of an iteration are dealt round-robin to the CTAs; each
+// CTA keeps its OWN copy of pts[] (target cloud + prices) in shared memory and sweeps all n candidates for
+// its bidders with its 1024 threads; everything else (list, bids, assignment maps) lives in rank 0's shared
+// memory and is read / written by the other ranks through distributed shared memory.  Rank 0 resolves the
+// iteration (GetMax + Assign) and broadcasts the new prices into every copy.  Two cluster barriers per
+// iteration (~0.2 us each) replace nothing in the reference: its seven launches per iteration stay gone.
+// Results are bit-identical to the single-CTA kernel (same per-bidder arithmetic, same tie rules).
+template <int kC>
+__global__ void __launch_bounds__(kEmdThreads, 1) emd_auction_cluster_kernel(const EmdArgs A) {
+    namespace cg = cooperative_groups;
+    cg::cluster_group cluster = cg::this_cluster();
+    extern __shared__ __align__(16) unsigned sm_u[];
+    __shared__ int s_cnt;
+    __shared__ Top2 s_merge[kEmdThreads / 32];  // per-warp partials of this CTA
+    __shared__ Top2 s_fin[kEmdSmall];           // rank 0: final per-bidder results of the small path
+    const int n = A.n, tid = threadIdx.x;
+    const int rank = (int)cluster.block_rank();
+    const int n_clusters = gridDim.x / kC;
+    // local copy of the candidates; master state on rank 0 (generic pointers into its shared memory)
+    float4 *pts = reinterpret_cast<float4 *>(sm_u);
+    unsigned *base0 = cluster.map_shared_rank(sm_u, 0);
+    float *max_inc = reinterpret_cast<float *>(base0 + 4 * (size_t)n);
+    float *bid_inc = max_inc + n;
+    int *max_idx = reinterpret_cast<int *>(bid_inc + n);
+    int *ainv = max_idx + n;
+    int *asg = ainv + n;
+    int *bid = asg + n;
+    int *sec = bid + n;
+    int *list = sec + n;
+    int *m_cnt = cluster.map_shared_rank(&s_cnt, 0);
+    Top2 *m_fin = cluster.map_shared_rank(s_fin, 0);
+    for (int b = blockIdx.x / kC; b < A.B; b += n_clusters) {
+        const float *x1 = A.xyz1 + (size_t)b * n * 3;
+        const float *x2g = A.xyz2 + (size_t)b * n * 3;
+        for (int k = tid; k < n; k += kEmdThreads) {
+            pts[k] = make_float4(x2g[3 * k], x2g[3 * k + 1], x2g[3 * k + 2], 0.f);
+            if (rank == 0) {
+                max_inc[k] = 0.f; max_idx[k] = INT_MAX; ainv[k] = -1; asg[k] = -1; bid[k] = -1; sec[k] = -1;
+            }
+        }
+        int used = 0;
+        bool have_list = false;
+        for (int it = 0; it < A.iters; ++it) {
+            const bool last = it == A.iters - 1;
+            if (!have_list && rank == 0) {
+                if (tid == 0) s_cnt = 0;
+                __syncthreads();
+                for (int j = tid; j < n; j += kEmdThreads)
+                    if (asg[j] == -1) list[atomicAdd(&s_cnt, 1)] = j;
+            }
+            cluster.sync();  // list, count, prices of every copy and the hints are in place
+            const int U = *m_cnt;
+            if (U == 0) break;
+            ++used;
+            // ---- Bid: this CTA's bidders are p = rank, rank + kC, ...
+            const int Ur = U > rank ? (U - rank + kC - 1) / kC : 0;
+            const bool small = U <= kEmdSmall;  // then Ur <= 8 and G >= 128: one round, warp partials
+            int G = kEmdThreads;
+            if (Ur > 0) { G = 1; while (G * 2 * Ur <= kEmdThreads) G *= 2; }
+            if (!small && G > 32) G = 32;  // the array path finishes a bidder inside one warp
+            const int groups = kEmdThreads / G;
+            const int lane_g = tid & (G - 1);
+            const int w = G < 32 ? G : 32;
+            for (int q0 = 0; q0 < Ur; q0 += groups) {
+                const int q = q0 + tid / G;
+                const bool valid = q < Ur;
+                const int j = valid ? list[q * kC + rank] : 0;
+                const Top2 t = sweep_bidder(valid, j, valid ? bid[j] : -1, valid ? sec[j] : -1, x1, pts, n,
+                                            lane_g, G, w);
+                if (small) {
+                    if ((tid & 31) == 0) s_merge[tid >> 5] = t;
+                } else if (valid && lane_g == 0) {
+                    const float inc = __fadd_rn(__fsub_rn(t.best, t.better), A.eps);
+                    bid[j] = t.i;
+                    sec[j] = t.i2;
+                    bid_inc[j] = inc;
+                    atomicMax(reinterpret_cast<int *>(max_inc) + t.i, __float_as_int(inc));
+                }
+            }
+            if (small && Ur > 0) {
+                // this CTA's warp 0 finishes its bidders (G / 32 warp partials each) and posts them to rank 0
+                __syncthreads();
+                if (tid < 32) {
+                    Top2 t = s_merge[tid];
+                    const int wb = G >> 5;
+                    for (int o = wb >> 1; o > 0; o >>= 1) t = merge(t, shfl_xor(t, o));
+                    if (tid % wb == 0 && tid / wb < Ur) m_fin[(tid / wb) * kC + rank] = t;
+                }
+            }
+            cluster.sync();  // every bid of the iteration has reached rank 0
+            have_list = small;
+            if (rank != 0) continue;
+            if (small) {
+                // ---- GetMax + Assign inside warp 0 of rank 0, lane = bidder (as in the single-CTA kernel)
+                if (tid < 32) {
+                    const int lane = tid;
+                    const Top2 t = s_fin[lane];
+                    const bool bidder = lane < U;
+                    const int j = bidder ? list[lane] : -1;
+                    const int o = bidder ? t.i : -1 - lane;
+                    const float inc = __fadd_rn(__fsub_rn(t.best, t.better), A.eps);
+                    float mx = inc;
+                    for (int q = 0; q < U; ++q) {
+                        const int oq = __shfl_sync(0xffffffffu, o, q);
+                        const float iq = __shfl_sync(0xffffffffu, inc, q);
+                        if (oq == o && iq > mx) mx = iq;
+                    }
+                    const bool qual = (double)inc - 1e-6 <= (double)mx && (double)mx <= (double)inc + 1e-6;
+                    bool win = qual;
+                    for (int q = 0; q < U; ++q) {
+                        const int oq = __shfl_sync(0xffffffffu, o, q);
+                        const int jq = __shfl_sync(0xffffffffu, j, q);
+                        const bool qq = __shfl_sync(0xffffffffu, (int)qual, q) != 0;
+                        if (oq == o && qq && jq < j) win = false;
+                    }
+                    win = bidder && (win || last);
+                    int item = -1;
+                    if (bidder) { bid[j] = t.i; sec[j] = t.i2; }
+                    if (win) {
+                        const int prev = ainv[o];
+                        if (!last && prev != -1) { asg[prev] = -1; item = prev; }
+                        ainv[o] = j;
+                        asg[j] = o;
+                        const float np = __fadd_rn(pts[o].w, inc);
+#pragma unroll
+                        for (int r = 0; r < kC; ++r) cluster.map_shared_rank(pts, r)[o].w = np;
+                    } else if (bidder) {
+                        item = j;
+                    }
+                    const unsigned has = __ballot_sync(0xffffffffu, item != -1);
+                    __syncwarp();
+                    if (item != -1) list[__popc(has & ((1u << lane) - 1))] = item;
+                    if (lane == 0) s_cnt = __popc(has);
+                }
+                continue;
+            }
+            // ---- GetMax / Assign over the arrays (more than 32 bidders), rank 0 only
+            for (int p = tid; p < U; p += kEmdThreads) {
+                const int j = list[p], o = bid[j];
+                const double bi = (double)bid_inc[j], mx = (double)max_inc[o];
+                if (bi - 1e-6 <= mx && mx <= bi + 1e-6) atomicMin(max_idx + o, j);
+            }
+            __syncthreads();
+            for (int p = tid; p < U; p += kEmdThreads) {
+                const int j = list[p], o = bid[j];
+                if (last || max_idx[o] == j) {
+                    const int prev = ainv[o];
+                    if (!last && prev != -1) asg[prev] = -1;
+                    ainv[o] = j;
+                    asg[j] = o;
+                    const float np = __fadd_rn(pts[o].w, bid_inc[j]);
+#pragma unroll
+                    for (int r = 0; r < kC; ++r) cluster.map_shared_rank(pts, r)[o].w = np;
+                    max_inc[o] = -1e9f;
+                    max_idx[o] = INT_MAX;
+                }
+            }
+            __syncthreads();
+        }
+        cluster.sync();  // rank 0 is done writing into the other copies; its state is final
+        if (rank == 0) {
+            for (int j = tid; j < n; j += kEmdThreads) {
+                const int k = asg[j];
+                const float dx = __fsub_rn(x1[3 * j], x2g[3 * k]), dy = __fsub_rn(x1[3 * j + 1], x2g[3 * k + 1]),
+                            dz = __fsub_rn(x1[3 * j + 2], x2g[3 * k + 2]);
+                A.dist[(size_t)b * n + j] = __fmaf_rn(dz, dz, __fmaf_rn(dx, dx, __fmul_rn(dy, dy)));
+                A.assignment[(size_t)b * n + j] = k;
+            }
+            if (A.iters_used && tid == 0) A.iters_used[b] = used;
+        }
+        cluster.sync();  // nobody re-initialises its copy while rank 0 still reads or others still write
+    }
+}
+
 // emd_cuda_backward (:270-305): only xyz1 receives a gradient; every point owns its row.
 __global__ void __launch_bounds__(256) emd_grad_kernel(const float *__restrict__ xyz1,
                                                        const float *__restrict__ xyz2,
@@ -319,6 +504,32 @@ extern "C" int houv_emd_forward(const float *xyz1, const float *xyz2, int B, int
     a.xyz1 = xyz1; a.xyz2 = xyz2; a.dist = dist; a.assignment = assignment; a.iters_used = iters_used;
     a.ws = (unsigned *)workspace; a.B = B; a.n = n; a.iters = iters; a.eps = eps;
     const int grid = B < 148 * 4 ? B : 148 * 4;
+    // small batches: a cluster of 4 CTAs per element (HOUV_EMD_CLUSTER=0 turns it off, =1 forces it)
+    const int cl = getenv("HOUV_EMD_CLUSTER") ? atoi(getenv("HOUV_EMD_CLUSTER")) : -1;
+    constexpr int kC = 4;
+    if (n <= kEmdSmemN && n >= 256 && (cl == 1 || (cl < 0 && B * kC <= 148))) {
+        static bool attr_set = false;
+        if (!attr_set) {
+            cudaError_t e = cudaFuncSetAttribute(emd_auction_cluster_kernel<kC>,
+                                                 cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                 (int)(sizeof(unsigned) * kEmdWords * kEmdSmemN));
+            if (e != cudaSuccess) return (int)e;
+            attr_set = true;
+        }
+        cudaLaunchConfig_t cfg = {};
+        const int clusters = B < 32 ? B : 32;
+        cfg.gridDim = dim3(clusters * kC);
+        cfg.blockDim = dim3(kEmdThreads);
+        cfg.dynamicSmemBytes = sizeof(unsigned) * kEmdWords * (size_t)n;
+        cfg.stream = (cudaStream_t)stream;
+        cudaLaunchAttribute attr;
+        attr.id = cudaLaunchAttributeClusterDimension;
+        attr.val.clusterDim.x = kC; attr.val.clusterDim.y = 1; attr.val.clusterDim.z = 1;
+        cfg.attrs = &attr;
+        cfg.numAttrs = 1;
+        cudaError_t e = cudaLaunchKernelEx(&cfg, emd_auction_cluster_kernel<kC>, a);
+        return e == cudaSuccess ? check_launch() : (int)e;
+    }
     if (n <= kEmdSmemN) {
         static bool attr_set = false;
         if (!attr_set) {
