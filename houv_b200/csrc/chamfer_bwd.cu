@@ -233,14 +233,8 @@ static int backward_impl(const float *xyz1, const float *xyz2, const float *grad
         const int per_sm = (int)((227 * 1024) / (res_bytes + 1024));
         int grid = 148 * (per_sm < 1 ? 1 : per_sm > 2 ? 2 : per_sm);  // registers allow 2 x 512 threads
         if (grid > B) grid = B;
-        static bool attr_set = false;
-        if (!attr_set) {
-            cudaError_t e = cudaFuncSetAttribute(grad_resident_kernel,
-                                                 cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                                 200 * 1024);
-            if (e != cudaSuccess) return (int)e;
-            attr_set = true;
-        }
+        static unsigned long long smem_set = 0;  // per-device flag bits
+        if (int e = ensure_dyn_smem(grad_resident_kernel, 200 * 1024, smem_set)) return e;
         grad_resident_kernel<<<grid, kResThreads, res_bytes, (cudaStream_t)stream>>>(a, B, assign);
         return check_launch();
     }

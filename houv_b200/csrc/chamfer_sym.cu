@@ -337,14 +337,8 @@ int sym_col_splits(int B, int nr, int nc) {
 // B*nc 64-bit words, required when nr > kSRows; a.row_keys: B*nr words, required when
 // sym_col_splits() > 1.
 int launch_chamfer_sym(const SymArgs &a, cudaStream_t st) {
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(chamfer_sym_kernel<8>,
-                                             cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                             (int)sizeof(SmemK1s));
-        if (e != cudaSuccess) return (int)e;
-        attr_set = true;
-    }
+    static unsigned long long smem_set = 0;  // per-device flag bits
+    if (int e = ensure_dyn_smem(chamfer_sym_kernel<8>, (int)sizeof(SmemK1s), smem_set)) return e;
     const int chunks = (a.nr + kSRows - 1) / kSRows;
     const int splits = sym_col_splits(a.B, a.nr, a.nc);
     SymArgs k = a;

@@ -57,6 +57,20 @@ int launch_chamfer_sym(const SymArgs &a, cudaStream_t st);
 // columns as well so that the grid covers the GPU.  Shared by the launcher and the workspace size.
 int sym_col_splits(int B, int nr, int nc);
 
+// cudaFuncAttributeMaxDynamicSharedMemorySize is a per-device attribute: set it once per device and
+// call site (`done` = the call site's bit mask of devices already configured).
+template <class F>
+inline int ensure_dyn_smem(F *func, int bytes, unsigned long long &done) {
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return (int)e;
+    if (dev < 64 && ((done >> dev) & 1ull)) return 0;
+    e = cudaFuncSetAttribute(func, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+    if (e != cudaSuccess) return (int)e;
+    if (dev < 64) done |= 1ull << dev;
+    return 0;
+}
+
 inline int check_launch() {
     cudaError_t e = cudaGetLastError();
     return e == cudaSuccess ? 0 : (int)e;

@@ -508,14 +508,10 @@ extern "C" int houv_emd_forward(const float *xyz1, const float *xyz2, int B, int
     const int cl = getenv("HOUV_EMD_CLUSTER") ? atoi(getenv("HOUV_EMD_CLUSTER")) : -1;
     constexpr int kC = 4;
     if (n <= kEmdSmemN && n >= 256 && (cl == 1 || (cl < 0 && B * kC <= 148))) {
-        static bool attr_set = false;
-        if (!attr_set) {
-            cudaError_t e = cudaFuncSetAttribute(emd_auction_cluster_kernel<kC>,
-                                                 cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                                 (int)(sizeof(unsigned) * kEmdWords * kEmdSmemN));
-            if (e != cudaSuccess) return (int)e;
-            attr_set = true;
-        }
+        static unsigned long long smem_set = 0;  // per-device flag bits
+        if (int e = ensure_dyn_smem(emd_auction_cluster_kernel<kC>,
+                                    (int)(sizeof(unsigned) * kEmdWords * kEmdSmemN), smem_set))
+            return e;
         cudaLaunchConfig_t cfg = {};
         const int clusters = B < 32 ? B : 32;
         cfg.gridDim = dim3(clusters * kC);
@@ -531,14 +527,10 @@ extern "C" int houv_emd_forward(const float *xyz1, const float *xyz2, int B, int
         return e == cudaSuccess ? check_launch() : (int)e;
     }
     if (n <= kEmdSmemN) {
-        static bool attr_set = false;
-        if (!attr_set) {
-            cudaError_t e = cudaFuncSetAttribute(emd_auction_kernel<true>,
-                                                 cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                                 (int)(sizeof(unsigned) * kEmdWords * kEmdSmemN));
-            if (e != cudaSuccess) return (int)e;
-            attr_set = true;
-        }
+        static unsigned long long smem_set = 0;  // per-device flag bits
+        if (int e = ensure_dyn_smem(emd_auction_kernel<true>,
+                                    (int)(sizeof(unsigned) * kEmdWords * kEmdSmemN), smem_set))
+            return e;
         emd_auction_kernel<true><<<grid, kEmdThreads, sizeof(unsigned) * kEmdWords * (size_t)n, (cudaStream_t)stream>>>(a);
     } else {
         emd_auction_kernel<false><<<grid, kEmdThreads, 0, (cudaStream_t)stream>>>(a);

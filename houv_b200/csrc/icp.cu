@@ -212,13 +212,8 @@ extern "C" int houv_icp(const float *src, const float *tgt, int P, int N, int M,
     a.src = src; a.tgt = tgt; a.init = init; a.T_out = T_out; a.stats = stats;
     a.P = P; a.N = N; a.M = M; a.init_per_pair = init_per_pair; a.max_iter = max_iteration;
     a.max_dist = max_distance; a.rel_fitness = relative_fitness; a.rel_rmse = relative_rmse;
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(icp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                             (int)sizeof(IcpSmem));
-        if (e != cudaSuccess) return (int)e;
-        attr_set = true;
-    }
+    static unsigned long long smem_set = 0;  // per-device flag bits
+    if (int e = ensure_dyn_smem(icp_kernel, (int)sizeof(IcpSmem), smem_set)) return e;
     icp_kernel<<<P, kIcpThreads, sizeof(IcpSmem), (cudaStream_t)stream>>>(a);
     return check_launch();
 }

@@ -213,13 +213,8 @@ extern "C" int houv_idam_step(const float *src, const float *tgt, const void *co
     a.w_out = weights_out;
     a.B = B; a.N = N; a.M = M;
     const size_t smem = sizeof(float) * 7 * (size_t)N;
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(idam_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                             (int)(sizeof(float) * 7 * kStepMaxN));
-        if (e != cudaSuccess) return (int)e;
-        attr_set = true;
-    }
+    static unsigned long long smem_set = 0;  // per-device flag bits
+    if (int e = ensure_dyn_smem(idam_step_kernel, (int)(sizeof(float) * 7 * kStepMaxN), smem_set)) return e;
     int blocks = B < 148 * 8 ? B : 148 * 8;
     idam_step_kernel<<<blocks, kStepThreads, smem, (cudaStream_t)stream>>>(a);
     return check_launch();

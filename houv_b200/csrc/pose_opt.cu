@@ -418,14 +418,8 @@ constexpr int kDefaultPoseVariant = 12;  // 0..5: two directed scans (this file)
 
 template <int kQ, int H, int U>
 static int launch_pose(const PoseArgs &a, cudaStream_t st) {
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(pose_kernel<kQ, H, U>,
-                                             cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                             (int)sizeof(Smem));
-        if (e != cudaSuccess) return (int)e;
-        attr_set = true;
-    }
+    static unsigned long long smem_set = 0;  // per-device flag bits
+    if (int e = ensure_dyn_smem(pose_kernel<kQ, H, U>, (int)sizeof(Smem), smem_set)) return e;
     pose_kernel<kQ, H, U><<<a.rows, kThreads, sizeof(Smem), st>>>(a);
     return check_launch();
 }

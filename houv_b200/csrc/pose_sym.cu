@@ -509,14 +509,8 @@ __global__ void __launch_bounds__(kSymThreads, 1) pose_sym_kernel(const PoseArgs
 
 template <int kU, int kRG, int kNM>
 static int launch_sym(const PoseArgs &a, cudaStream_t st) {
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(pose_sym_kernel<kU, kRG, kNM>,
-                                             cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                             (int)sizeof(SmemSym));
-        if (e != cudaSuccess) return (int)e;
-        attr_set = true;
-    }
+    static unsigned long long smem_set = 0;  // per-device flag bits
+    if (int e = ensure_dyn_smem(pose_sym_kernel<kU, kRG, kNM>, (int)sizeof(SmemSym), smem_set)) return e;
     pose_sym_kernel<kU, kRG, kNM><<<a.rows, kSymThreads, sizeof(SmemSym), st>>>(a);
     return check_launch();
 }
