@@ -45,18 +45,36 @@ __device__ __forceinline__ double det3(const double (&M)[3][3]) {
 }
 
 // H = U S V^T (S descending).  Returns R = V diag(1,1,sign) U^T with det R = +1.
-__device__ inline void kabsch_from_covariance(const double (&H)[3][3], double (&R)[3][3]) {
+// warm: optional orthogonal matrix to start the iteration from (in/out: the V found).  A caller that
+// solves a slowly changing H again and again (ICP) then needs one or two sweeps instead of six or seven.
+__device__ inline void kabsch_from_covariance(const double (&H)[3][3], double (&R)[3][3],
+                                              double (*warm)[3] = nullptr) {
     double A[3][3], V[3][3];
 #pragma unroll
     for (int i = 0; i < 3; ++i)
 #pragma unroll
-        for (int j = 0; j < 3; ++j) { A[i][j] = H[i][j]; V[i][j] = i == j ? 1.0 : 0.0; }
+        for (int j = 0; j < 3; ++j) {
+            V[i][j] = warm ? warm[i][j] : (i == j ? 1.0 : 0.0);
+            A[i][j] = H[i][j];
+        }
+    if (warm) {
+#pragma unroll
+        for (int i = 0; i < 3; ++i)
+#pragma unroll
+            for (int j = 0; j < 3; ++j) A[i][j] = H[i][0] * V[0][j] + H[i][1] * V[1][j] + H[i][2] * V[2][j];
+    }
     for (int sweep = 0; sweep < 30; ++sweep) {
         bool rotated = false;
         jacobi_pair(A, V, 0, 1, rotated);
         jacobi_pair(A, V, 0, 2, rotated);
         jacobi_pair(A, V, 1, 2, rotated);
         if (!rotated) break;
+    }
+    if (warm) {
+#pragma unroll
+        for (int i = 0; i < 3; ++i)
+#pragma unroll
+            for (int j = 0; j < 3; ++j) warm[i][j] = V[i][j];
     }
     // A = U S (columns), sort columns by norm, descending
     double sg[3];

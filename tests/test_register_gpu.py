@@ -166,6 +166,31 @@ def test_icp_vs_float64_oracle():
     assert reg2.transformation.shape == (P, 4, 4) and torch.isfinite(reg2.transformation).all()
 
 
+@pytest.mark.gpu
+@pytest.mark.parametrize("case", [(6, 2048, 2048, 0.02), (5, 1500, 2000, 0.03), (3, 700, 300, 0.05),
+                                  (4, 2048, 2048, 0.2)])
+def test_icp_grid_search_equals_full_scan(case, monkeypatch):
+    """The uniform-grid neighbour search (cells >= 1.01 x radius, 3 x 3 x 3 cells per query) gives bit for
+    bit the transformation, fitness, rmse, iteration count and correspondence count of the scan over all
+    target points, on MVP-shaped pairs, ragged sizes, duplicated target points (equal distances: lowest
+    index) and a radius large enough that some pairs fall back to the scan."""
+    from houv_b200.icp import TRANS_INIT, registration_icp
+    P, N, M, radius = case
+    s, t, _ = synth.make_pairs(7, P, n_points=max(N, M))
+    s, t = s[:, :N].copy(), t[:, :M].copy()
+    t[:, 1::7] = t[:, 0:-1:7][:, : t[:, 1::7].shape[1]]  # duplicates
+    src, tgt = torch.from_numpy(s).cuda(), torch.from_numpy(t).cuda()
+    out = {}
+    for grid in ("1", "0"):
+        monkeypatch.setenv("HOUV_ICP_GRID", grid)
+        reg = registration_icp(src, tgt, radius, TRANS_INIT, 60)
+        out[grid] = (reg.transformation.cpu(), reg.fitness.cpu(), reg.inlier_rmse.cpu(), reg.iterations.cpu(),
+                     reg.correspondences.cpu())
+    for a, b in zip(out["1"], out["0"]):
+        assert torch.equal(a, b)
+    assert float(out["1"][4].max()) > 0
+
+
 def test_icp_no_correspondences_keeps_init():
     from houv_b200.icp import registration_icp
     src = torch.rand(2, 64, 3).cuda()
