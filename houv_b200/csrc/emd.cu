@@ -524,7 +524,10 @@ extern "C" int houv_emd_forward(const float *xyz1, const float *xyz2, int B, int
         cfg.attrs = &attr;
         cfg.numAttrs = 1;
         cudaError_t e = cudaLaunchKernelEx(&cfg, emd_auction_cluster_kernel<kC>, a);
-        return e == cudaSuccess ? check_launch() : (int)e;
+        if (e == cudaSuccess) return check_launch();
+        // a partition that cannot co-schedule 4 such CTAs (MIG slice, MPS limit): the one-CTA kernel below
+        (void)cudaGetLastError();
+        if (cl == 1) return (int)e;
     }
     if (n <= kEmdSmemN) {
         static unsigned long long smem_set = 0;  // per-device flag bits
