@@ -280,7 +280,9 @@ __global__ void __launch_bounds__(kSThreads, 2) chamfer_sym_kernel(const SymArgs
                 }
             }
             // ---- rows improved in this tile: exact first arg-min inside the winning superblock
-            if (scan_active) {
+            //      (with column slices the recovery is deferred: only the winning slice's superblock
+            //      has to be searched, once, by chamfer_sym_unpack)
+            if (scan_active && !A.row_keys) {
 #pragma unroll
                 for (int r = 0; r < 8; ++r) {
                     if (dirty & (1u << r)) {
@@ -297,9 +299,9 @@ __global__ void __launch_bounds__(kSThreads, 2) chamfer_sym_kernel(const SymArgs
             const int i = row0 + r;
             if (i < nrows) {
                 const size_t o = (size_t)b * nr + rbase + i;
-                if (A.row_keys) {
+                if (A.row_keys) {  // smallest distance, then earliest superblock: it holds the first minimum
                     atomicMin(A.row_keys + o, ((unsigned long long)__float_as_uint(best[r]) << 32) |
-                                                  (unsigned)idxr[r]);
+                                                  (unsigned)gid[r]);
                 } else {
                     A.dist_r[o] = best[r];
                     A.idx_r[o] = idxr[r];
@@ -309,25 +311,53 @@ __global__ void __launch_bounds__(kSThreads, 2) chamfer_sym_kernel(const SymArgs
     }
 }
 
-__global__ void chamfer_sym_unpack(const unsigned long long *keys, float *dist, int *idx, size_t n,
-                                   const unsigned long long *keys2, float *dist2, int *idx2, size_t n2) {
-    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) {  // second segment
-        i -= n;
-        if (i >= n2) return;
-        keys = keys2; dist = dist2; idx = idx2;
+// Column keys hold (distance, row index); row keys hold (distance, superblock of 64 columns): the row's
+// first minimum is the first column of that superblock whose distance equals the minimum.  Blocks
+// [0, col_blocks) unpack 256 column keys each, the others recover 8 rows each, one warp per row (the 64
+// candidates are 768 contiguous bytes; lane l looks at candidates 2l and 2l+1).
+__global__ void __launch_bounds__(256) chamfer_sym_unpack(const unsigned long long *keys, float *dist, int *idx,
+                                                         size_t n, unsigned col_blocks,
+                                                         const unsigned long long *row_keys, float *dist_r,
+                                                         int *idx_r, size_t n_r, const float *rows,
+                                                         const float *cols, int nr, int nc) {
+    if (blockIdx.x < col_blocks) {
+        const size_t i = (size_t)blockIdx.x * 256 + threadIdx.x;
+        if (i < n) {
+            const unsigned long long k = keys[i];
+            dist[i] = __uint_as_float((unsigned)(k >> 32));
+            idx[i] = (int)(unsigned)(k & 0xffffffffull);
+        }
+        return;
     }
-    const unsigned long long k = keys[i];
-    dist[i] = __uint_as_float((unsigned)(k >> 32));
-    idx[i] = (int)(unsigned)(k & 0xffffffffull);
+    const size_t i = (size_t)(blockIdx.x - col_blocks) * 8 + (threadIdx.x >> 5);
+    if (i >= n_r) return;
+    const int lane = threadIdx.x & 31;
+    const unsigned long long k = row_keys[i];
+    const float target = __uint_as_float((unsigned)(k >> 32));
+    const int j0 = (int)(unsigned)(k & 0xffffffffull) * kSGrp;
+    const size_t b = i / nr;
+    const float qx = __ldg(rows + 3 * i), qy = __ldg(rows + 3 * i + 1), qz = __ldg(rows + 3 * i + 2);
+    const float *c = cols + (b * nc + j0) * 3;
+    const int m = min(kSGrp, nc - j0);
+    bool hit0 = false, hit1 = false;
+    if (2 * lane < m)
+        hit0 = sqdist_ref(__ldg(c + 6 * lane), __ldg(c + 6 * lane + 1), __ldg(c + 6 * lane + 2), qx, qy, qz) == target;
+    if (2 * lane + 1 < m)
+        hit1 = sqdist_ref(__ldg(c + 6 * lane + 3), __ldg(c + 6 * lane + 4), __ldg(c + 6 * lane + 5), qx, qy, qz) == target;
+    const unsigned any = __ballot_sync(0xffffffffu, hit0 || hit1);
+    if (lane == 0) {
+        dist_r[i] = target;
+        idx_r[i] = j0;  // a row that never improved (no finite distance) keeps the superblock's first index
+    }
+    if (any && lane == __ffs(any) - 1) idx_r[i] = j0 + 2 * lane + (hit0 ? 0 : 1);
 }
 
 int sym_col_splits(int B, int nr, int nc) {
     static const int forced = getenv("HOUV_K1S_SPLIT") ? atoi(getenv("HOUV_K1S_SPLIT")) : 0;
     const long long ctas = (long long)((nr + kSRows - 1) / kSRows) * B;
-    // one CTA per SM: slices narrower than that pay the per-CTA row recovery too often (measured, C2:
-    // 4 slices 68.6 us, 8 slices 72.7 us, directed kernel 74.7 us)
-    int s = forced > 0 ? forced : (ctas >= 148 ? 1 : (int)(148 / ctas));
+    // two CTAs per SM (measured, C2 = 32 x 2048^2: 8 slices 66.6 us, 4 slices 68.6 us, directed kernel
+    // 74.7 us; batches that already fill the GPU lose from slicing, C5: 0.71 ms with 4 slices, 0.665 without)
+    int s = forced > 0 ? forced : (ctas >= 148 ? 1 : (int)(296 / ctas));
     const int most = nc / 256;  // at least 256 columns per slice
     if (s > most) s = most;
     return s < 1 ? 1 : s;
@@ -355,8 +385,10 @@ int launch_chamfer_sym(const SymArgs &a, cudaStream_t st) {
     chamfer_sym_kernel<8><<<grid, kSThreads, sizeof(SmemK1s), st>>>(k);
     if (int err = check_launch()) return err;
     if (n_c + n_r) {
-        chamfer_sym_unpack<<<(unsigned)((n_c + n_r + 255) / 256), 256, 0, st>>>(
-            k.keys, a.dist_c, a.idx_c, n_c, k.row_keys, a.dist_r, a.idx_r, n_r);
+        const unsigned col_blocks = (unsigned)((n_c + 255) / 256), row_blocks = (unsigned)((n_r + 7) / 8);
+        chamfer_sym_unpack<<<col_blocks + row_blocks, 256, 0, st>>>(k.keys, a.dist_c, a.idx_c, n_c, col_blocks,
+                                                                   k.row_keys, a.dist_r, a.idx_r, n_r, a.rows,
+                                                                   a.cols, a.nr, a.nc);
         return check_launch();
     }
     return 0;
