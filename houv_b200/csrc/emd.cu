@@ -28,6 +28,7 @@ namespace houv {
 constexpr int kEmdThreads = 1024;
 constexpr int kEmdSmall = 32;    // bidders resolved inside one warp
 constexpr int kEmdWords = 12;    // state words per point
+constexpr int kEmdPtsN = 12288;   // candidates (16 B/point) still in shared memory up to here
 constexpr int kEmdSmemN = 4096;   // 48 B/point of state in shared memory up to here
 
 struct EmdArgs {
@@ -136,7 +137,9 @@ __device__ __forceinline__ Top2 sweep_bidder(bool valid, int j, int o1, int o2, 
 // prices packed so that one 16-byte load feeds a candidate evaluation, then max_inc, bid_inc, max_idx,
 // ainv, asg, bid, sec, list.  kSmem: the block lives in dynamic shared memory (pointers provably shared,
 // so LDS/STS/ATOMS); otherwise in the caller's workspace.
-template <bool kSmem>
+// kPts (only meaningful when !kSmem): the state is in the workspace but pts[] still fits shared memory
+// (16 B per point, n <= 12288), which keeps the sweep's candidate loads on chip.
+template <bool kSmem, bool kPts = kSmem>
 __global__ void __launch_bounds__(kEmdThreads, 1) emd_auction_kernel(const EmdArgs A) {
     extern __shared__ __align__(16) unsigned sm_u[];
     __shared__ int s_cnt;
@@ -144,7 +147,7 @@ __global__ void __launch_bounds__(kEmdThreads, 1) emd_auction_kernel(const EmdAr
     const int n = A.n, tid = threadIdx.x;
     for (int b = blockIdx.x; b < A.B; b += gridDim.x) {
         unsigned *base = kSmem ? sm_u : A.ws + (size_t)b * kEmdWords * n;  // 16-byte aligned (12 words)
-        float4 *pts = reinterpret_cast<float4 *>(base);
+        float4 *pts = reinterpret_cast<float4 *>(kPts ? sm_u : base);
         float *max_inc = reinterpret_cast<float *>(base + 4 * (size_t)n);
         float *bid_inc = max_inc + n;
         int *max_idx = reinterpret_cast<int *>(bid_inc + n);
@@ -535,8 +538,13 @@ extern "C" int houv_emd_forward(const float *xyz1, const float *xyz2, int B, int
                                     (int)(sizeof(unsigned) * kEmdWords * kEmdSmemN), smem_set))
             return e;
         emd_auction_kernel<true><<<grid, kEmdThreads, sizeof(unsigned) * kEmdWords * (size_t)n, (cudaStream_t)stream>>>(a);
+    } else if (n <= kEmdPtsN) {
+        static unsigned long long smem_set = 0;  // per-device flag bits
+        if (int e = ensure_dyn_smem(emd_auction_kernel<false, true>, (int)(sizeof(float4) * kEmdPtsN), smem_set))
+            return e;
+        emd_auction_kernel<false, true><<<grid, kEmdThreads, sizeof(float4) * (size_t)n, (cudaStream_t)stream>>>(a);
     } else {
-        emd_auction_kernel<false><<<grid, kEmdThreads, 0, (cudaStream_t)stream>>>(a);
+        emd_auction_kernel<false, false><<<grid, kEmdThreads, 0, (cudaStream_t)stream>>>(a);
     }
     return check_launch();
 }

@@ -25,7 +25,7 @@ def _clouds(B, n, seed, quant=None):
     (2, 64, 0.005, 50, None), (3, 1024, 0.005, 50, None), (2, 2048, 0.002, 3000, None),
     (1, 777, 0.004, 200, None), (2, 1, 0.005, 5, None), (1, 3, 0.005, 1, None),
     (2, 512, 0.005, 300, 8), (1, 2048, 0.005, 50, 16), (1, 4096, 0.005, 20, None),
-    (2, 5000, 0.005, 12, None), (300, 128, 0.005, 100, None), (40, 1024, 0.005, 60, None), (35, 512, 0.005, 40, None),
+    (2, 5000, 0.005, 12, None), (300, 128, 0.005, 100, None), (40, 1024, 0.005, 60, None), (35, 512, 0.005, 40, None), (1, 12500, 0.005, 6, None),
     (3, 300, 0.003, 400, None)])
 @pytest.mark.parametrize("cluster", ["0", "1"], ids=["one-cta", "cluster4"])
 def test_forward_bit_exact_vs_oracle(case, cluster, monkeypatch):
