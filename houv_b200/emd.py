@@ -26,9 +26,9 @@ def emd_forward(xyz1, xyz2, eps, iters, want_iters=False):
     xyz1, xyz2 = xyz1.contiguous(), xyz2.contiguous()
     B, n, _ = xyz1.shape
     dev = xyz1.device
-    dist = torch.zeros(B, n, device=dev)
-    assignment = torch.full((B, n), -1, device=dev, dtype=torch.int32)
-    used = torch.zeros(B, device=dev, dtype=torch.int32) if want_iters else None
+    dist = torch.empty(B, n, device=dev)  # every element is written by the kernel
+    assignment = torch.empty(B, n, device=dev, dtype=torch.int32)
+    used = torch.empty(B, device=dev, dtype=torch.int32) if want_iters else None
     lib = _lib.load()
     need = lib.houv_emd_workspace_bytes(B, n)
     ws = torch.empty(need, dtype=torch.uint8, device=dev) if need else None
