@@ -303,7 +303,10 @@ __global__ void __launch_bounds__(kEmdThreads, 1) emd_auction_kernel(const EmdAr
 // iteration (GetMax + Assign) and broadcasts the new prices into every copy.  Two cluster barriers per
 // iteration (~0.2 us each) replace nothing in the reference: its seven launches per iteration stay gone.
 // Results are bit-identical to the single-CTA kernel (same per-bidder arithmetic, same tie rules).
-template <int kC>
+// kState: the master state sits in rank 0's shared memory (n <= 4096); otherwise in the caller's workspace
+// (global memory, visible to every rank after the cluster barriers) while every CTA still keeps its own
+// copy of pts[] in shared memory (n <= 12288).
+template <int kC, bool kState>
 __global__ void __launch_bounds__(kEmdThreads, 1) emd_auction_cluster_kernel(const EmdArgs A) {
     namespace cg = cooperative_groups;
     cg::cluster_group cluster = cg::this_cluster();
@@ -316,18 +319,18 @@ __global__ void __launch_bounds__(kEmdThreads, 1) emd_auction_cluster_kernel(con
     const int n_clusters = gridDim.x / kC;
     // local copy of the candidates; master state on rank 0 (generic pointers into its shared memory)
     float4 *pts = reinterpret_cast<float4 *>(sm_u);
-    unsigned *base0 = cluster.map_shared_rank(sm_u, 0);
-    float *max_inc = reinterpret_cast<float *>(base0 + 4 * (size_t)n);
-    float *bid_inc = max_inc + n;
-    int *max_idx = reinterpret_cast<int *>(bid_inc + n);
-    int *ainv = max_idx + n;
-    int *asg = ainv + n;
-    int *bid = asg + n;
-    int *sec = bid + n;
-    int *list = sec + n;
     int *m_cnt = cluster.map_shared_rank(&s_cnt, 0);
     Top2 *m_fin = cluster.map_shared_rank(s_fin, 0);
     for (int b = blockIdx.x / kC; b < A.B; b += n_clusters) {
+        unsigned *base0 = kState ? cluster.map_shared_rank(sm_u, 0) : A.ws + (size_t)b * kEmdWords * n;
+        float *max_inc = reinterpret_cast<float *>(base0 + 4 * (size_t)n);
+        float *bid_inc = max_inc + n;
+        int *max_idx = reinterpret_cast<int *>(bid_inc + n);
+        int *ainv = max_idx + n;
+        int *asg = ainv + n;
+        int *bid = asg + n;
+        int *sec = bid + n;
+        int *list = sec + n;
         const float *x1 = A.xyz1 + (size_t)b * n * 3;
         const float *x2g = A.xyz2 + (size_t)b * n * 3;
         for (int k = tid; k < n; k += kEmdThreads) {
@@ -510,25 +513,29 @@ extern "C" int houv_emd_forward(const float *xyz1, const float *xyz2, int B, int
     // small batches: a cluster of 4 CTAs per element (HOUV_EMD_CLUSTER=0 turns it off, =1 forces it)
     const int cl = getenv("HOUV_EMD_CLUSTER") ? atoi(getenv("HOUV_EMD_CLUSTER")) : -1;
     constexpr int kC = 4;
-    if (n <= kEmdSmemN && n >= 256 && (cl == 1 || (cl < 0 && B * kC <= 148))) {
-        static unsigned long long smem_set = 0;  // per-device flag bits
-        if (int e = ensure_dyn_smem(emd_auction_cluster_kernel<kC>,
-                                    (int)(sizeof(unsigned) * kEmdWords * kEmdSmemN), smem_set))
+    if (n <= kEmdPtsN && n >= 256 && (cl == 1 || (cl < 0 && B * kC <= 148))) {
+        const bool state_smem = n <= kEmdSmemN;
+        static unsigned long long set_a = 0, set_b = 0;  // per-device flag bits
+        if (int e = ensure_dyn_smem(emd_auction_cluster_kernel<kC, true>,
+                                    (int)(sizeof(unsigned) * kEmdWords * kEmdSmemN), set_a))
+            return e;
+        if (int e = ensure_dyn_smem(emd_auction_cluster_kernel<kC, false>, (int)(sizeof(float4) * kEmdPtsN), set_b))
             return e;
         cudaLaunchConfig_t cfg = {};
         const int clusters = B < 32 ? B : 32;
         cfg.gridDim = dim3(clusters * kC);
         cfg.blockDim = dim3(kEmdThreads);
-        cfg.dynamicSmemBytes = sizeof(unsigned) * kEmdWords * (size_t)n;
+        cfg.dynamicSmemBytes = state_smem ? sizeof(unsigned) * kEmdWords * (size_t)n : sizeof(float4) * (size_t)n;
         cfg.stream = (cudaStream_t)stream;
         cudaLaunchAttribute attr;
         attr.id = cudaLaunchAttributeClusterDimension;
         attr.val.clusterDim.x = kC; attr.val.clusterDim.y = 1; attr.val.clusterDim.z = 1;
         cfg.attrs = &attr;
         cfg.numAttrs = 1;
-        cudaError_t e = cudaLaunchKernelEx(&cfg, emd_auction_cluster_kernel<kC>, a);
+        cudaError_t e = state_smem ? cudaLaunchKernelEx(&cfg, emd_auction_cluster_kernel<kC, true>, a)
+                                   : cudaLaunchKernelEx(&cfg, emd_auction_cluster_kernel<kC, false>, a);
         if (e == cudaSuccess) return check_launch();
-        // a partition that cannot co-schedule 4 such CTAs (MIG slice, MPS limit): the one-CTA kernel below
+        // a partition that cannot co-schedule 4 such CTAs (MIG slice, MPS limit): the one-CTA kernels below
         (void)cudaGetLastError();
         if (cl == 1) return (int)e;
     }
