@@ -14,6 +14,7 @@ import math
 import torch
 
 from .chamfer import cd, fscore
+from .emd import calc_emd, emd  # noqa: F401  (model_utils_completion.py:170-175 lives beside calc_cd)
 
 
 def calc_cd(output, gt, calc_f1=False):
