@@ -473,6 +473,8 @@ extern "C" int houv_pose_optimise_ex(const HouvPoseProblem *q, void *stream) {
         case 13: return launch_pose_sym(a, 84, st);
         case 14: return launch_pose_sym(a, 44, st);
         case 15: return launch_pose_sym(a, 1004, st);  // four-metric sweep even when wview == 0
+        case 16: return launch_pose_sym(a, 1008, st);  // variant 12 with the (distance, index) recovery
+        case 17: return launch_pose_sym(a, 1009, st);  // ... with it only where no minimum is stored
         case 1: return launch_pose<4, 1, 2>(a, st);
         case 2: return launch_pose<4, 2, 1>(a, st);
         case 3: return launch_pose<2, 1, 2>(a, st);

@@ -31,6 +31,8 @@
 //
 // Everything after the scan (radix select of the k-th smallest, the min() side selection,
 // gradient through the winning side, closed-form pose backward, Adam) is as in pose_opt.cu.
+#include <type_traits>
+
 #include "pose_common.cuh"
 
 namespace houv {
@@ -133,8 +135,21 @@ __device__ __forceinline__ void sym_step(const float2 X, const float2 Y, const f
     }
 }
 
-// kSymUnroll: unroll of the 8 rotation steps of a phase
-template <int kSymUnroll, int kRG, int kNM>
+// Arg-min recovery: step k of a lane's walk over the 32 candidate pairs of a 64-wide group visits
+// pair (k + lane) & 31; bit k of mx / my says the .x / .y candidate of that step equals the minimum.
+// -> offset (0..63) of the smallest matching candidate inside the group, 0 when nothing matched.
+__device__ __forceinline__ int first_match(unsigned mx, unsigned my, int lane) {
+    mx = __funnelshift_l(mx, mx, lane);  // rotate: bit k -> bit (k + lane) & 31 = pair index
+    my = __funnelshift_l(my, my, lane);
+    const int fx = mx ? 2 * (__ffs(mx) - 1) : 128, fy = my ? 2 * (__ffs(my) - 1) + 1 : 128;
+    const int f = min(fx, fy);
+    return f < 128 ? f : 0;
+}
+
+// kSymUnroll: unroll of the 8 rotation steps of a phase; kRecov: arg-min recovery -- 0 = running
+// (distance, index) search everywhere; 1 = equality with the stored minimum where there is one;
+// 2 = 1 + elsewhere candidates evaluated once into registers, minimum by FMNMX3, then equality
+template <int kSymUnroll, int kRG, int kNM, int kRecov>
 __global__ void __launch_bounds__(kSymThreads, 1) pose_sym_kernel(const PoseArgs A) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     SmemSym &S = *reinterpret_cast<SmemSym *>(smem_raw);
@@ -337,6 +352,18 @@ __global__ void __launch_bounds__(kSymThreads, 1) pose_sym_kernel(const PoseArgs
 #pragma unroll
             for (int dir = 0; dir < 2; ++dir) {
                 const int len = dir ? N : M;
+                if (shift == 24) {
+                    // sign + 7 exponent bits: a cloud's distances share one or two values, so the
+                    // lanes of a warp would queue on the same counter -- one add per distinct digit
+                    for (int q0 = 0; q0 < len; q0 += kSymThreads) {
+                        const int q = q0 + t;
+                        const unsigned bin = q < len ? __float_as_uint(S.d3[dir][q]) >> 24 : 256u;
+                        const unsigned peers = __match_any_sync(0xffffffffu, bin);
+                        if (bin < 256u && (t & 31) == __ffs(peers) - 1)
+                            atomicAdd(&S.hist[dir][bin], __popc(peers));
+                    }
+                    continue;
+                }
                 for (int q = t; q < len; q += kSymThreads) {
                     const unsigned bits = __float_as_uint(S.d3[dir][q]);
                     const bool match = (shift == 24) ||
@@ -444,33 +471,84 @@ __global__ void __launch_bounds__(kSymThreads, 1) pose_sym_kernel(const PoseArgs
 #pragma unroll
         for (int m = 0; m < kNM; ++m) {
             if (m > 0 && A.wview == 0.f) continue;  // loss = w3d*min_1 only (train_utils.py:439)
-            const int dir = side[m];
+            auto side_grad = [&](auto dirc) {
+            constexpr int dir = decltype(dirc)::value;  // compile-time: smem bases become immediates
             // x, y, z of a cloud are consecutive kPts-float arrays: one base pointer per cloud
             const float *qB = dir ? S.yx : S.tx, *tB = dir ? S.tx : S.yx;
             const int nq = dir ? N : M;
             // d(mean over rows)/d(row) * weight / k      houv.py:124,222; m_u_c.py:94-95
             const float coef = gscale * (m == 0 ? A.w3d : A.wview) / (float)(m == 0 ? k3d : N);
+            // The minimum itself is still on chip for the 3-D metric (d3) and for every row metric
+            // (the two halves' shadows hold their final row minima): there the candidates are
+            // searched for EQUALITY with it (smallest matching index), which needs no running
+            // (distance, index) pair.  Column minima of the view metrics were only summed.
+            const bool known = kRecov >= 1 && (m == 0 || dir == 1);
             for (int q = t; q < nq; q += kSymThreads) {
                 float wt = 1.f;
+                float bd = kInf;
                 if (m == 0) {  // top-k membership of the trimmed 3-D term
                     const float d = S.d3[dir][q];
                     wt = d < thr[dir] ? 1.f : (d == thr[dir] ? tiew[dir] : 0.f);
                     if (wt == 0.f) continue;
+                    bd = d;
+                } else if (known) {
+                    const int uq = q >> 3, rq = q & 7;
+                    const int slot = ((2 * m + (rq >> 2)) ^ (uq & 7)) * 4 + (rq & 3);
+                    const float *sh = reinterpret_cast<const float *>(&S.shadow[0][0]);
+                    bd = fminf(sh[uq * 32 + slot], sh[(uq + 256) * 32 + slot]);
                 }
                 const int j0 = (int)S.gid[m][dir][q] * kSB;
+                const unsigned j0b = (unsigned)j0 * 4u, lane8 = (unsigned)lane * 8u;
+                const char *tb = reinterpret_cast<const char *>(tB);
                 const float qx = qB[q], qy = qB[kPts + q], qz = qB[2 * kPts + q];
-                float bd = kInf;
                 int bj = j0;
+                if (known) {
+                    unsigned mx = 0u, my = 0u;  // bit k: the pair visited at step k equals the minimum
+#pragma unroll
+                    for (int k = 0; k < kSB / 2; ++k) {
+                        // byte offset of pair (k + lane) & 31 of the group: one add, one and-or
+                        const unsigned off = ((lane8 + 8u * k) & 248u) | j0b;
+                        const float2 X = *reinterpret_cast<const float2 *>(tb + off);
+                        const float2 Y = *reinterpret_cast<const float2 *>(tb + 4 * kPts + off);
+                        const float2 Z = *reinterpret_cast<const float2 *>(tb + 8 * kPts + off);
+                        const float2 d = metric_dist2(m, X, Y, Z, qx, qy, qz);
+                        if (d.x == bd) mx |= 1u << k;
+                        if (d.y == bd) my |= 1u << k;
+                    }
+                    bj = j0 + first_match(mx, my, lane);  // a match always exists unless bd is NaN
+                } else if (kRecov == 2) {
+                    float2 dv[kSB / 2];
+#pragma unroll
+                    for (int k = 0; k < kSB / 2; ++k) {
+                        const unsigned off = ((lane8 + 8u * k) & 248u) | j0b;
+                        const float2 X = *reinterpret_cast<const float2 *>(tb + off);
+                        const float2 Y = *reinterpret_cast<const float2 *>(tb + 4 * kPts + off);
+                        const float2 Z = *reinterpret_cast<const float2 *>(tb + 8 * kPts + off);
+                        dv[k] = metric_dist2(m, X, Y, Z, qx, qy, qz);
+                    }
+                    bd = kInf;
+#pragma unroll
+                    for (int k = 0; k < kSB / 2; ++k) bd = min3(bd, dv[k].x, dv[k].y);
+                    unsigned mx = 0u, my = 0u;
+#pragma unroll
+                    for (int k = 0; k < kSB / 2; ++k) {
+                        if (dv[k].x == bd) mx |= 1u << k;
+                        if (dv[k].y == bd) my |= 1u << k;
+                    }
+                    bj = j0 + first_match(mx, my, lane);
+                } else {
+                    bd = kInf;
 #pragma unroll 4
-                for (int k = 0; k < kSB / 2; ++k) {
-                    const int c = j0 + 2 * ((k + lane) & (kSB / 2 - 1));
-                    const float2 X = *reinterpret_cast<const float2 *>(&tB[c]);
-                    const float2 Y = *reinterpret_cast<const float2 *>(&tB[kPts + c]);
-                    const float2 Z = *reinterpret_cast<const float2 *>(&tB[2 * kPts + c]);
-                    const float2 d = metric_dist2(m, X, Y, Z, qx, qy, qz);
-                    // first minimum = lexicographic minimum of (distance, index)
-                    if (d.x < bd || (d.x == bd && c < bj)) { bd = d.x; bj = c; }
-                    if (d.y < bd || (d.y == bd && c + 1 < bj)) { bd = d.y; bj = c + 1; }
+                    for (int k = 0; k < kSB / 2; ++k) {
+                        const int c = j0 + 2 * ((k + lane) & (kSB / 2 - 1));
+                        const float2 X = *reinterpret_cast<const float2 *>(&tB[c]);
+                        const float2 Y = *reinterpret_cast<const float2 *>(&tB[kPts + c]);
+                        const float2 Z = *reinterpret_cast<const float2 *>(&tB[2 * kPts + c]);
+                        const float2 d = metric_dist2(m, X, Y, Z, qx, qy, qz);
+                        // first minimum = lexicographic minimum of (distance, index)
+                        if (d.x < bd || (d.x == bd && c < bj)) { bd = d.x; bj = c; }
+                        if (d.y < bd || (d.y == bd && c + 1 < bj)) { bd = d.y; bj = c + 1; }
+                    }
                 }
                 // sqrt backward then chamfer backward (x2): d=0 gives inf*0 = NaN like autograd
                 const float gg = (coef * wt) / (2.f * sqrtf(bd)) * 2.f;
@@ -486,6 +564,9 @@ __global__ void __launch_bounds__(kSymThreads, 1) pose_sym_kernel(const PoseArgs
                 acc[6] += v2 * x0; acc[7] += v2 * x1; acc[8] += v2 * x2;
                 acc[9] += v0; acc[10] += v1; acc[11] += v2;
             }
+            };
+            if (side[m]) side_grad(std::integral_constant<int, 1>{});
+            else side_grad(std::integral_constant<int, 0>{});
         }
         block_sum_sym<12>(acc, S);
 
@@ -507,16 +588,21 @@ __global__ void __launch_bounds__(kSymThreads, 1) pose_sym_kernel(const PoseArgs
     if (t == 0) state_store(st, A, row);
 }
 
-template <int kU, int kRG, int kNM>
+template <int kU, int kRG, int kNM, int kRecov = 2>
 static int launch_sym(const PoseArgs &a, cudaStream_t st) {
     static unsigned long long smem_set = 0;  // per-device flag bits
-    if (int e = ensure_dyn_smem(pose_sym_kernel<kU, kRG, kNM>, (int)sizeof(SmemSym), smem_set)) return e;
-    pose_sym_kernel<kU, kRG, kNM><<<a.rows, kSymThreads, sizeof(SmemSym), st>>>(a);
+    if (int e = ensure_dyn_smem(pose_sym_kernel<kU, kRG, kNM, kRecov>, (int)sizeof(SmemSym), smem_set))
+        return e;
+    pose_sym_kernel<kU, kRG, kNM, kRecov><<<a.rows, kSymThreads, sizeof(SmemSym), st>>>(a);
     return check_launch();
 }
 
 int launch_pose_sym(const PoseArgs &a, int unroll, cudaStream_t st) {
     // a loss without view terms (wview == 0: train_utils.getPredict_angle) needs the 3-D metric only
+    if (unroll == 1008)  // the (distance, index) recovery everywhere: kept to test the others against
+        return a.wview == 0.f ? launch_sym<8, 2, 1, 0>(a, st) : launch_sym<8, 2, 4, 0>(a, st);
+    if (unroll == 1009)  // equality search where the minimum is stored, (distance, index) elsewhere
+        return a.wview == 0.f ? launch_sym<8, 2, 1, 1>(a, st) : launch_sym<8, 2, 4, 1>(a, st);
     if (a.wview == 0.f && unroll != 1004) return launch_sym<8, 2, 1>(a, st);
     switch (unroll) {
         case 4: return launch_sym<4, 2, 4>(a, st);

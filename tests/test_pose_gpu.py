@@ -189,3 +189,31 @@ def test_bad_arguments_raise():
     big = torch.rand(1, 4096, 3).cuda()
     with pytest.raises(RuntimeError):
         solver.pose_optimise(big, big, p, KERNEL, 1)  # > 2048 points
+
+
+@pytest.mark.parametrize("n,iters,kw", [(256, 6, {}), (333, 4, {}), (2048, 3, {}),
+                                        (512, 5, dict(wview=0.0, w3d=6.0))])
+def test_equality_argmin_recovery_equals_distance_index_search(pose_variant, n, iters, kw):
+    """K3 symmetric recovers an arg-min from the winning 64-wide group by searching it for EQUALITY
+    with the minimum: the one still on chip (3-D metric, every row metric) or, for column minima of
+    the view metrics, the FMNMX3 minimum of the candidates evaluated once into registers.  Variant 16
+    is the same kernel with the running (distance, index) search everywhere, 17 with it only where no
+    minimum is stored.  Same first-minimum index (chamfer3D.cu:36,46,126) => every trace value,
+    parameter and Adam moment identical bit for bit, duplicated points included."""
+    if pose_variant != 12:
+        pytest.skip("compares the two recoveries of the symmetric kernel")
+    from houv_b200 import _lib
+    lib = _lib.load()
+    src, tgt, _ = _pairs(11, 2, n=n)
+    src[:, 5] = src[:, 4]      # exact ties inside a group ...
+    tgt[:, n - 1] = tgt[:, 3]  # ... and across groups
+    res = []
+    for variant in (12, 16, 17):
+        lib.houv_set_pose_variant(variant)
+        out, params, m, v = _gpu_run(src, tgt, iters, **kw)
+        res.append((out["trace"].clone(), out["min_1"].clone(), out["R"].clone(), out["T"].clone(),
+                    params.clone(), m.clone(), v.clone()))
+    lib.houv_set_pose_variant(12)
+    for other in res[1:]:
+        for a, b in zip(res[0], other):
+            assert torch.equal(a, b)
