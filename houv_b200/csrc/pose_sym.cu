@@ -29,6 +29,8 @@
 //  * threads 0..255 sweep the lower half of the superblocks, threads 256..511 the upper half
 //    with the same rows; the two row results are merged with the lower half winning ties.
 //
+// The one-metric instantiation (kNM = 1) uses 107 KB and 64 registers: two CTAs per SM.
+//
 // Everything after the scan (radix select of the k-th smallest, the min() side selection,
 // gradient through the winning side, closed-form pose backward, Adam) is as in pose_opt.cu.
 #include <type_traits>
@@ -41,18 +43,23 @@ constexpr int kSymThreads = 512;
 constexpr int kSB = 64;        // columns per superblock = rows per sub-group = arg-min group width
 constexpr int kRowsPerThread = 8;
 
-struct SmemSym {
+// kNM = metrics swept (4: Predict_loss, 1: the 3-D term alone).  The four-metric layout fills an SM
+// (225 KB, one CTA); the one-metric layout is 107 KB so that two CTAs share an SM and one row's
+// select / recovery / pose phases run under the other row's sweep.
+template <int kNM>
+struct SmemSymT {
+    static constexpr int kSlots = 2 * kNM;  // float4 chunks of row minima per thread
     // NB the gradient phase addresses y and z as x + kPts and x + 2*kPts: keep the order
     float tx[kPts], ty[kPts], tz[kPts];   // target cloud (columns), fixed
     float yx[kPts], yy[kPts], yz[kPts];   // transformed source (rows) of this iteration
     float d3[2][kPts];                    // 3-D metric: [0] = column minima (dist1), [1] = row minima (dist2)
-    unsigned char gid[4][2][kPts];        // winning group: [m][0][col] = 64-row sub-group, [m][1][row] = superblock
-    unsigned char rgid1[4][kPts];         // rows: winning superblock seen by the upper column half
-    float part[2][32][4][kSB];            // [column half][sub-group][metric][column]: partial column minima
-    // row minima as of the last superblock boundary: per thread 8 float4 chunks, chunk c = values
-    // k = 4c..4c+3 (k = metric*8 + r), stored at position c ^ (thread & 7) so that the LDS.128 /
-    // STS.128 of 8 neighbouring threads hit 8 different bank groups
-    float4 shadow[kSymThreads][8];
+    unsigned char gid[kNM][2][kPts];      // winning group: [m][0][col] = 64-row sub-group, [m][1][row] = superblock
+    unsigned char rgid1[kNM][kPts];       // rows: winning superblock seen by the upper column half
+    float part[2][32][kNM][kSB];          // [column half][sub-group][metric][column]: partial column minima
+    // row minima as of the last superblock boundary: per thread kSlots float4 chunks, chunk c = values
+    // k = 4c..4c+3 (k = metric*8 + r), stored at position c ^ (thread & (kSlots-1)) so that the LDS.128 /
+    // STS.128 of neighbouring threads spread over the bank groups
+    float4 shadow[kSymThreads][kSlots];
     int hist[2][256];
     float red[kSymThreads / 32][16];
     float pose[12];
@@ -61,7 +68,7 @@ struct SmemSym {
     double bt[2];
 };
 
-template <int NV>
+template <int NV, class SmemSym>
 __device__ __forceinline__ void block_sum_sym(float (&v)[NV], SmemSym &S) {
 #pragma unroll
     for (int i = 0; i < NV; ++i) {
@@ -150,8 +157,10 @@ __device__ __forceinline__ int first_match(unsigned mx, unsigned my, int lane) {
 // (distance, index) search everywhere; 1 = equality with the stored minimum where there is one;
 // 2 = 1 + elsewhere candidates evaluated once into registers, minimum by FMNMX3, then equality
 template <int kSymUnroll, int kRG, int kNM, int kRecov>
-__global__ void __launch_bounds__(kSymThreads, 1) pose_sym_kernel(const PoseArgs A) {
+__global__ void __launch_bounds__(kSymThreads, kNM == 1 ? 2 : 1) pose_sym_kernel(const PoseArgs A) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
+    using SmemSym = SmemSymT<kNM>;
+    constexpr int kSwz = SmemSym::kSlots - 1;  // shadow chunk swizzle mask
     SmemSym &S = *reinterpret_cast<SmemSym *>(smem_raw);
     const int t = threadIdx.x;
     const int row = blockIdx.x;
@@ -225,10 +234,10 @@ __global__ void __launch_bounds__(kSymThreads, 1) pose_sym_kernel(const PoseArgs
         }
         // row bookkeeping of this sweep: shadow = +inf, winning superblock = 0
 #pragma unroll
-        for (int c = 0; c < 2 * kNM; ++c) S.shadow[t][c ^ (t & 7)] = make_float4(kInf, kInf, kInf, kInf);
-        for (int i = t; i < 4 * 2 * kPts / 4; i += kSymThreads)
+        for (int c = 0; c < 2 * kNM; ++c) S.shadow[t][c ^ (t & kSwz)] = make_float4(kInf, kInf, kInf, kInf);
+        for (int i = t; i < kNM * 2 * kPts / 4; i += kSymThreads)
             reinterpret_cast<unsigned *>(&S.gid[0][0][0])[i] = 0u;
-        for (int i = t; i < 4 * kPts / 4; i += kSymThreads)
+        for (int i = t; i < kNM * kPts / 4; i += kSymThreads)
             reinterpret_cast<unsigned *>(&S.rgid1[0][0])[i] = 0u;
         __syncthreads();
 
@@ -285,7 +294,7 @@ __global__ void __launch_bounds__(kSymThreads, 1) pose_sym_kernel(const PoseArgs
 #pragma unroll
                 for (int c = 0; c < 2 * kNM; ++c) {
                     const int m = c >> 1, r0 = 4 * (c & 1);
-                    float4 &slot = S.shadow[t][c ^ (t & 7)];
+                    float4 &slot = S.shadow[t][c ^ (t & kSwz)];
                     const float4 pv = slot;
                     improved |= (best[m][r0 + 0] < pv.x ? 1u : 0u) << (4 * c + 0);
                     improved |= (best[m][r0 + 1] < pv.y ? 1u : 0u) << (4 * c + 1);
@@ -328,7 +337,7 @@ __global__ void __launch_bounds__(kSymThreads, 1) pose_sym_kernel(const PoseArgs
                 for (int r = 0; r < 8; ++r) {
                     const int i = row0 + r;
                     float b = best[m][r];
-                    const float4 o4 = S.shadow[t + 256][(2 * m + (r >> 2)) ^ (t & 7)];  // (t+256)&7 == t&7
+                    const float4 o4 = S.shadow[t + 256][(2 * m + (r >> 2)) ^ (t & kSwz)];  // (t+256)&7 == t&7
                     const float b1 = (r & 3) == 0 ? o4.x : (r & 3) == 1 ? o4.y : (r & 3) == 2 ? o4.z : o4.w;
                     if (b1 < b) {
                         b = b1;
@@ -493,9 +502,9 @@ __global__ void __launch_bounds__(kSymThreads, 1) pose_sym_kernel(const PoseArgs
                     bd = d;
                 } else if (known) {
                     const int uq = q >> 3, rq = q & 7;
-                    const int slot = ((2 * m + (rq >> 2)) ^ (uq & 7)) * 4 + (rq & 3);
+                    const int slot = ((2 * m + (rq >> 2)) ^ (uq & kSwz)) * 4 + (rq & 3);
                     const float *sh = reinterpret_cast<const float *>(&S.shadow[0][0]);
-                    bd = fminf(sh[uq * 32 + slot], sh[(uq + 256) * 32 + slot]);
+                    bd = fminf(sh[uq * (8 * kNM) + slot], sh[(uq + 256) * (8 * kNM) + slot]);
                 }
                 const int j0 = (int)S.gid[m][dir][q] * kSB;
                 const unsigned j0b = (unsigned)j0 * 4u, lane8 = (unsigned)lane * 8u;
@@ -591,9 +600,9 @@ __global__ void __launch_bounds__(kSymThreads, 1) pose_sym_kernel(const PoseArgs
 template <int kU, int kRG, int kNM, int kRecov = 2>
 static int launch_sym(const PoseArgs &a, cudaStream_t st) {
     static unsigned long long smem_set = 0;  // per-device flag bits
-    if (int e = ensure_dyn_smem(pose_sym_kernel<kU, kRG, kNM, kRecov>, (int)sizeof(SmemSym), smem_set))
+    if (int e = ensure_dyn_smem(pose_sym_kernel<kU, kRG, kNM, kRecov>, (int)sizeof(SmemSymT<kNM>), smem_set))
         return e;
-    pose_sym_kernel<kU, kRG, kNM, kRecov><<<a.rows, kSymThreads, sizeof(SmemSym), st>>>(a);
+    pose_sym_kernel<kU, kRG, kNM, kRecov><<<a.rows, kSymThreads, sizeof(SmemSymT<kNM>), st>>>(a);
     return check_launch();
 }
 
