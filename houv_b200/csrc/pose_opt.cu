@@ -414,7 +414,7 @@ __global__ void __launch_bounds__(kThreads, 2) pose_kernel(const PoseArgs A) {
 }
 
 static int g_pose_variant = -1;
-constexpr int kDefaultPoseVariant = 12;  // 0..5: two directed scans (this file); 10: symmetric scan (pose_sym.cu)
+constexpr int kDefaultPoseVariant = 13;  // 0..5: two directed scans (this file); 10: symmetric scan (pose_sym.cu)
 
 template <int kQ, int H, int U>
 static int launch_pose(const PoseArgs &a, cudaStream_t st) {

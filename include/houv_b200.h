@@ -204,7 +204,7 @@ int houv_set_nn_variant(int variant);
  * different unrolls, identical results among themselves and equal to 0..5 up to the summation
  * order of the loss terms; 15 = 12 with the four-metric sweep forced when wview == 0; 16 = 12
  * with the (distance, index) arg-min recovery everywhere instead of the equality search (both
- * bit-identical to 12); -1 = default (12, or $HOUV_POSE_VARIANT).  Returns the old value. */
+ * bit-identical to 12); -1 = default (13, or $HOUV_POSE_VARIANT).  Returns the old value. */
 int houv_set_pose_variant(int variant);
 
 /* FP32 CUDA-core peak probe: runs `iters` x 64 FFMA (or FFMA2 when packed) per thread on a

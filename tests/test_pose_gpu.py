@@ -23,7 +23,7 @@ N_SMALL = 256
 KERNEL = 32
 
 
-@pytest.fixture(autouse=True, params=[12, 0], ids=["k3-symmetric", "k3-two-scans"])
+@pytest.fixture(autouse=True, params=[13, 0], ids=["k3-symmetric", "k3-two-scans"])
 def pose_variant(request):
     """Every test of this module runs against both K3 kernels: the symmetric scan
     (csrc/pose_sym.cu, the default) and the two-directed-scans kernel (csrc/pose_opt.cu)."""
@@ -200,7 +200,7 @@ def test_equality_argmin_recovery_equals_distance_index_search(pose_variant, n, 
     is the same kernel with the running (distance, index) search everywhere, 17 with it only where no
     minimum is stored.  Same first-minimum index (chamfer3D.cu:36,46,126) => every trace value,
     parameter and Adam moment identical bit for bit, duplicated points included."""
-    if pose_variant != 12:
+    if pose_variant != 13:
         pytest.skip("compares the two recoveries of the symmetric kernel")
     from houv_b200 import _lib
     lib = _lib.load()
@@ -208,12 +208,12 @@ def test_equality_argmin_recovery_equals_distance_index_search(pose_variant, n, 
     src[:, 5] = src[:, 4]      # exact ties inside a group ...
     tgt[:, n - 1] = tgt[:, 3]  # ... and across groups
     res = []
-    for variant in (12, 16, 17):
+    for variant in (13, 12, 16, 17):
         lib.houv_set_pose_variant(variant)
         out, params, m, v = _gpu_run(src, tgt, iters, **kw)
         res.append((out["trace"].clone(), out["min_1"].clone(), out["R"].clone(), out["T"].clone(),
                     params.clone(), m.clone(), v.clone()))
-    lib.houv_set_pose_variant(12)
+    lib.houv_set_pose_variant(13)
     for other in res[1:]:
         for a, b in zip(res[0], other):
             assert torch.equal(a, b)

@@ -209,7 +209,7 @@ def test_icp_batch_metrics_shape():
     assert torch.isfinite(ans).all()
 
 
-@pytest.mark.parametrize("variant", [12, 0])
+@pytest.mark.parametrize("variant", [13, 0])
 def test_merged_batches_equal_batch_by_batch(variant):
     """shard.register_pairs launches every batch's first pass together and every batch's retries
     together (solver.solve_model_batches, per-row gradient scale): bit-identical poses to calling

@@ -13,7 +13,7 @@ from tests.util import load_npz
 pytestmark = pytest.mark.gpu
 
 
-@pytest.fixture(autouse=True, params=[12, 0], ids=["k3-symmetric", "k3-two-scans"])
+@pytest.fixture(autouse=True, params=[13, 0], ids=["k3-symmetric", "k3-two-scans"])
 def pose_variant(request):
     from houv_b200 import _lib
     lib = _lib.load()
