@@ -612,7 +612,8 @@ int launch_pose_sym(const PoseArgs &a, int unroll, cudaStream_t st) {
         return a.wview == 0.f ? launch_sym<8, 2, 1, 0>(a, st) : launch_sym<8, 2, 4, 0>(a, st);
     if (unroll == 1009)  // equality search where the minimum is stored, (distance, index) elsewhere
         return a.wview == 0.f ? launch_sym<8, 2, 1, 1>(a, st) : launch_sym<8, 2, 4, 1>(a, st);
-    if (a.wview == 0.f && unroll != 1004) return launch_sym<8, 2, 1>(a, st);
+    if (a.wview == 0.f && unroll != 1004)
+        return unroll == 84 ? launch_sym<8, 4, 1>(a, st) : launch_sym<8, 2, 1>(a, st);
     switch (unroll) {
         case 4: return launch_sym<4, 2, 4>(a, st);
         case 8: case 1004: return launch_sym<8, 2, 4>(a, st);

@@ -150,7 +150,7 @@ def cmd_solve():
     def run():
         solver.pose_optimise(src, tgt, init.clone(), 64, iters, lr=0.1, wview=0.0, tran_scale=1.0,
                              tran_offset=0.0)
-    for v in (12, 15):
+    for v in (12, 13, 15):
         _lib.load().houv_set_pose_variant(v)
         med, best = timeit(run, iters=3, warmup=1)
         print(json.dumps({"variant": v, "ms": round(med, 2),
