@@ -52,6 +52,8 @@ def parse():
     ap.add_argument("--pairs-per-gpu", type=int, default=150)
     ap.add_argument("--iters", type=int, default=ITERS, help="Adam iterations (reference: 200)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-balance", action="store_true",
+                    help="keep every rank's retry rows on that rank (no exchange inside the step)")
     return ap.parse_args()
 
 
@@ -164,7 +166,10 @@ def workload_config(args):
                         "its + angle_base 1-3 retries above 0.030" %
                         (args.pairs_per_gpu, KERNEL, args.iters),
             "pairs_per_gpu": args.pairs_per_gpu, "batch_size": BATCH, "starts": KERNEL,
-            "iters": args.iters, "points": N_POINTS, "parallelism": "pairs sharded, dp%d" % args.gpus,
+            "iters": args.iters, "points": N_POINTS, "parallelism": "pairs sharded, dp%d%s" % (
+                args.gpus, "" if args.gpus == 1 or args.no_balance else
+                "; retry rows of all ranks dealt evenly between the two launches of a step "
+                "(3 small all-gathers), none inside the 200-iteration loops"),
             "l2": "256 MB buffer written between timed steps (L2 flush)"}
 
 
@@ -231,9 +236,11 @@ def run_ours(args):
     d_src, d_tgt, d_gt = h_src.to(dev), h_tgt.to(dev), h_gt.to(dev)
     flush = torch.zeros(64 * 1024 * 1024, device=dev)  # 256 MB > 126 MB L2
 
+    balance = world > 1 and not args.no_balance  # retry rows of all ranks dealt evenly (solver._balanced_retry)
+
     def step_device():
         ans, met = shard.register_pairs(d_src, d_tgt, d_gt, batch_size=BATCH, kernel=KERNEL,
-                                        num_epochs=args.iters)
+                                        num_epochs=args.iters, balance=balance)
         return shard.gather_results(ans, met, world)
 
     def step_e2e():
@@ -241,7 +248,7 @@ def run_ours(args):
         b = h_tgt.to(dev, non_blocking=True)
         g = h_gt.to(dev, non_blocking=True)
         ans, met = shard.register_pairs(a, b, g, batch_size=BATCH, kernel=KERNEL,
-                                        num_epochs=args.iters)
+                                        num_epochs=args.iters, balance=balance)
         ans, met = shard.gather_results(ans, met, world)
         h_out.copy_(torch.cat([ans.reshape(-1, 16), met], dim=1), non_blocking=True)
         torch.cuda.current_stream().synchronize()

@@ -41,17 +41,18 @@ def init_distributed(backend=None):
 
 
 def register_pairs(src, tgt, transform=None, batch_size=50, kernel=64, num_epochs=200,
-                   solve=None):
+                   solve=None, balance=None):
     """Full HOUV registration (solve_model semantics) of src[P,N,3] -> tgt[P,N,3] in
     batches.  -> ans[P,4,4] and, when the ground truth is given, metrics[P,3] =
     (rotation error deg, translation error, mse) as train_HOUV.py:112-118 logs them.
-    `solve`: a solve_model-shaped callable to run batch by batch instead (the CPU tests pass one)."""
+    `solve`: a solve_model-shaped callable to run batch by batch instead (the CPU tests pass one).
+    `balance`: see solver.solve_model_batches (None = on under torch.distributed with > 1 rank)."""
     P = src.shape[0]
     if solve is None:
         # every batch's first pass in one launch, every batch's retries in a second one:
         # per-pair results identical to solve_model batch by batch (solver.solve_model_batches)
         ans = solver.solve_model_batches(src, tgt, batch_size=batch_size, kernel=kernel,
-                                         num_epochs=num_epochs)
+                                         num_epochs=num_epochs, balance=balance)
         met = None
         if transform is not None:
             met = torch.stack([rotation_error(ans[:, :3, :3], transform[:, :3, :3]),

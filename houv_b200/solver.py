@@ -269,13 +269,76 @@ def solve_model(net, src, src_rotated, pose=None, src_ori=None, tgt_ori=None, an
     return r_err, t_err, ans
 
 
-def solve_model_batches(src, src_rotated, batch_size=50, kernel=64, num_epochs=200):
+def _balanced_retry(srcF, tgtF, p_rows, pair_rows, base_rows, scale_rows, kernel, num_epochs):
+    """The retry launch of solve_model_batches with the rows of every rank dealt evenly over the
+    ranks (pairs are independent and so are rows: a row is its pair's two clouds, its initial
+    values, angle_base and gradient scale).  Three small all-gathers (NCCL): failed-pair counts +
+    clouds, row descriptions, row results.  -> dict(min_1, R, T) of THIS rank's rows, the same
+    bits pose_optimise would give for them locally."""
+    dist = torch.distributed
+    world, rank, dev = dist.get_world_size(), dist.get_rank(), srcF.device
+    n_l, N = srcF.shape[0], srcF.shape[1]
+    rows_l = sum(int(p.shape[0]) for p in p_rows)
+    cnt = torch.tensor([n_l, rows_l], device=dev, dtype=torch.int64)
+    cnts = torch.empty(world, 2, device=dev, dtype=torch.int64)
+    dist.all_gather_into_tensor(cnts, cnt)
+    cnts = cnts.cpu()
+    n_all, r_all = cnts[:, 0].tolist(), cnts[:, 1].tolist()
+    nmax, rmax, r_tot = max(n_all), max(r_all), sum(r_all)
+    empty = dict(min_1=torch.zeros(0, device=dev), R=torch.zeros(0, 3, 3, device=dev),
+                 T=torch.zeros(0, 3, device=dev))
+    if r_tot == 0:
+        return empty
+    # failed pairs of every rank, padded to nmax per rank: global pair index = rank*nmax + local
+    clouds = torch.zeros(2, nmax, N, 3, device=dev)
+    clouds[0, :n_l], clouds[1, :n_l] = srcF, tgtF
+    g_clouds = torch.empty(world, 2, nmax, N, 3, device=dev)
+    dist.all_gather_into_tensor(g_clouds, clouds)
+    g_src = g_clouds[:, 0].reshape(world * nmax, N, 3).contiguous()
+    g_tgt = g_clouds[:, 1].reshape(world * nmax, N, 3).contiguous()
+    # row descriptions [rmax, 11]: 8 initial values, pair (global), angle_base, gradient scale
+    desc = torch.zeros(rmax, 11, device=dev)
+    if rows_l:
+        desc[:rows_l, :8] = torch.cat(p_rows)
+        desc[:rows_l, 8] = (torch.cat(pair_rows) + rank * nmax).float()  # < 2^24: exact in float32
+        desc[:rows_l, 9] = torch.cat(base_rows).float()
+        desc[:rows_l, 10] = torch.cat(scale_rows)
+    g_desc = torch.empty(world, rmax, 11, device=dev)
+    dist.all_gather_into_tensor(g_desc, desc)
+    rows = torch.cat([g_desc[k, :r_all[k]] for k in range(world)])  # [r_tot, 11], rank-major
+    chunk = (r_tot + world - 1) // world
+    lo, hi = min(rank * chunk, r_tot), min((rank + 1) * chunk, r_tot)
+    res = torch.zeros(chunk, 13, device=dev)
+    if hi > lo:
+        mine = rows[lo:hi]
+        o = pose_optimise(g_src, g_tgt, mine[:, :8].contiguous(), kernel, num_epochs,
+                          row_pair=mine[:, 8].to(torch.int32).contiguous(),
+                          row_base=mine[:, 9].to(torch.int32).contiguous(),
+                          row_scale=mine[:, 10].contiguous())
+        res[:hi - lo, 0] = o["min_1"]
+        res[:hi - lo, 1:10] = o["R"].reshape(-1, 9)
+        res[:hi - lo, 10:13] = o["T"]
+    g_res = torch.empty(world * chunk, 13, device=dev)
+    dist.all_gather_into_tensor(g_res, res)  # rank k's rows [k*chunk, ...) = global rows in order
+    if rows_l == 0:
+        return empty
+    off = sum(r_all[:rank])
+    own = g_res[off:off + rows_l]
+    return dict(min_1=own[:, 0].contiguous(), R=own[:, 1:10].reshape(-1, 3, 3).contiguous(),
+                T=own[:, 10:13].contiguous())
+
+
+def solve_model_batches(src, src_rotated, batch_size=50, kernel=64, num_epochs=200, balance=None):
     """solve_model (houv.py:142-206) for a whole set of pairs walked in batches of `batch_size`
     as train_HOUV.py:100-112 does, with the SAME per-pair results as calling solve_model batch by
     batch -- initial values by position in the batch (houv.py:116), gradient scale 1/(rows of
     the batch) (:124), retries at angle_base 1..3 on each batch's own sub-batch (:154-180) -- but
     in TWO launches for the whole set (all first passes, then all retries) instead of two per
-    batch, which removes the partial last wave of every batch.  -> ans[P,4,4] on the device."""
+    batch, which removes the partial last wave of every batch.  -> ans[P,4,4] on the device.
+    `balance` (default: on when torch.distributed runs with more than one rank; every rank must
+    then call this together): the retry rows of ALL ranks are dealt evenly over the ranks before
+    the retry launch (_balanced_retry) -- same rows, same results, no rank waits for the one
+    whose shard has the most failed pairs."""
     src, src_rotated = src.float().contiguous(), src_rotated.float().contiguous()
     P, dev = src.shape[0], src.device
     if P == 0:
@@ -293,7 +356,10 @@ def solve_model_batches(src, src_rotated, batch_size=50, kernel=64, num_epochs=2
     rmse = rmse_loss.min(dim=1).values
     lst_add = torch.nonzero(rmse > RETRY_THRESHOLD).reshape(-1)  # ascending = batch order
     n_add = int(lst_add.numel())
-    if n_add > 0:
+    if balance is None:
+        balance = torch.distributed.is_available() and torch.distributed.is_initialized() \
+            and torch.distributed.get_world_size() > 1
+    if n_add > 0 or balance:
         batch_of = (lst_add // batch_size).cpu()
         counts = torch.bincount(batch_of, minlength=len(bounds)).tolist()
         p_rows, pair_rows, base_rows, scale_rows, first = [], [], [], [], 0
@@ -309,17 +375,21 @@ def solve_model_batches(src, src_rotated, batch_size=50, kernel=64, num_epochs=2
                 base_rows.append(torch.full((sub_rows,), b, device=dev, dtype=torch.int32))
                 scale_rows.append(torch.full((sub_rows,), 1.0 / sub_rows, device=dev))
             first += nb
-        out2 = pose_optimise(src[lst_add], src_rotated[lst_add], torch.cat(p_rows).contiguous(),
-                             kernel, num_epochs, row_pair=torch.cat(pair_rows).contiguous(),
-                             row_base=torch.cat(base_rows).contiguous(),
-                             row_scale=torch.cat(scale_rows).contiguous())
+        if balance:
+            out2 = _balanced_retry(src[lst_add], src_rotated[lst_add], p_rows, pair_rows, base_rows,
+                                   scale_rows, kernel, num_epochs)
+        else:
+            out2 = pose_optimise(src[lst_add], src_rotated[lst_add], torch.cat(p_rows).contiguous(),
+                                 kernel, num_epochs, row_pair=torch.cat(pair_rows).contiguous(),
+                                 row_base=torch.cat(base_rows).contiguous(),
+                                 row_scale=torch.cat(scale_rows).contiguous())
         # back to [angle_base][pair] order, then the reference's keep-if-better sequence
         order, off, first = [[], [], []], 0, 0
         for nb in counts:
             for b in range(3):
                 order[b].append(torch.arange(off, off + nb * kernel, device=dev))
                 off += nb * kernel
-        for b in range(3):
+        for b in range(3 if n_add > 0 else 0):
             sel = torch.cat(order[b])
             l_add = out2["min_1"][sel].reshape(n_add, kernel)
             R_add = out2["R"][sel].reshape(n_add, kernel, 3, 3)
