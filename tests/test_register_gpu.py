@@ -243,3 +243,35 @@ def test_merged_batches_equal_batch_by_batch(variant):
         assert 0 < retried  # the fixture does exercise the retry launch
     finally:
         _lib.load().houv_set_pose_variant(-1)
+
+
+def test_balanced_retry_equals_local_retry():
+    """solver._balanced_retry packs every rank's retry rows (clouds, initial values, pair, angle_base,
+    gradient scale), deals them over the ranks and returns each rank its own rows' results through three
+    all-gathers.  One rank here (NCCL, world size 1: the packing, the launch from the gathered arrays and the
+    unpacking are the same code); tools/balance_probe.py checks 2 and 8 ranks on a multi-GPU box
+    (profiles/r1_balance_probe_n2_session23.txt).  Identical poses to the local retry launch."""
+    import socket
+    import torch.distributed as dist
+    from houv_b200 import solver
+    if dist.is_initialized():
+        pytest.skip("a process group is already up")
+    with socket.socket() as sk:
+        sk.bind(("127.0.0.1", 0))
+        port = sk.getsockname()[1]
+    s, t, _ = synth.make_pairs(40, 7, n_points=192)
+    src, tgt = torch.from_numpy(s).cuda(), torch.from_numpy(t).cuda()
+    old = solver.RETRY_THRESHOLD
+    dist.init_process_group("nccl", init_method="tcp://127.0.0.1:%d" % port, world_size=1, rank=0,
+                            device_id=torch.device("cuda", torch.cuda.current_device()))
+    try:
+        solver.RETRY_THRESHOLD = 0.0  # every pair is retried, in all three batches
+        local = solver.solve_model_batches(src, tgt, batch_size=3, kernel=32, num_epochs=8, balance=False)
+        dealt = solver.solve_model_batches(src, tgt, batch_size=3, kernel=32, num_epochs=8, balance=True)
+        solver.RETRY_THRESHOLD = 1e9  # nobody is retried: the collective path must cope with zero rows
+        none_l = solver.solve_model_batches(src, tgt, batch_size=3, kernel=32, num_epochs=8, balance=False)
+        none_d = solver.solve_model_batches(src, tgt, batch_size=3, kernel=32, num_epochs=8, balance=True)
+    finally:
+        solver.RETRY_THRESHOLD = old
+        dist.destroy_process_group()
+    assert torch.equal(local, dealt) and torch.equal(none_l, none_d)
