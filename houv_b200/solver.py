@@ -341,7 +341,12 @@ def solve_model_batches(src, src_rotated, batch_size=50, kernel=64, num_epochs=2
     whose shard has the most failed pairs."""
     src, src_rotated = src.float().contiguous(), src_rotated.float().contiguous()
     P, dev = src.shape[0], src.device
+    if balance is None:
+        balance = torch.distributed.is_available() and torch.distributed.is_initialized() \
+            and torch.distributed.get_world_size() > 1
     if P == 0:
+        if balance:  # a rank without pairs still takes its share of the other ranks' retry rows
+            _balanced_retry(src, src_rotated, [], [], [], [], kernel, num_epochs)
         return torch.zeros(0, 4, 4, device=dev)
     bounds = [(l, min(l + batch_size, P)) for l in range(0, P, batch_size)]
     # row i of reset_weight's draws does not depend on the number of rows (initial_parameters)
@@ -356,9 +361,6 @@ def solve_model_batches(src, src_rotated, batch_size=50, kernel=64, num_epochs=2
     rmse = rmse_loss.min(dim=1).values
     lst_add = torch.nonzero(rmse > RETRY_THRESHOLD).reshape(-1)  # ascending = batch order
     n_add = int(lst_add.numel())
-    if balance is None:
-        balance = torch.distributed.is_available() and torch.distributed.is_initialized() \
-            and torch.distributed.get_world_size() > 1
     if n_add > 0 or balance:
         batch_of = (lst_add // batch_size).cpu()
         counts = torch.bincount(batch_of, minlength=len(bounds)).tolist()

@@ -271,7 +271,9 @@ def test_balanced_retry_equals_local_retry():
         solver.RETRY_THRESHOLD = 1e9  # nobody is retried: the collective path must cope with zero rows
         none_l = solver.solve_model_batches(src, tgt, batch_size=3, kernel=32, num_epochs=8, balance=False)
         none_d = solver.solve_model_batches(src, tgt, batch_size=3, kernel=32, num_epochs=8, balance=True)
+        empty = solver.solve_model_batches(src[:0], tgt[:0], batch_size=3, kernel=32, num_epochs=8, balance=True)
     finally:
         solver.RETRY_THRESHOLD = old
         dist.destroy_process_group()
     assert torch.equal(local, dealt) and torch.equal(none_l, none_d)
+    assert tuple(empty.shape) == (0, 4, 4)  # a rank without pairs still joins the exchange
