@@ -280,9 +280,9 @@ def _balanced_retry(srcF, tgtF, p_rows, pair_rows, base_rows, scale_rows, kernel
     n_l, N = srcF.shape[0], srcF.shape[1]
     rows_l = sum(int(p.shape[0]) for p in p_rows)
     cnt = torch.tensor([n_l, rows_l], device=dev, dtype=torch.int64)
-    cnts = torch.empty(world, 2, device=dev, dtype=torch.int64)
-    dist.all_gather_into_tensor(cnts, cnt)
-    cnts = cnts.cpu()
+    cnts = torch.empty(world * 2, device=dev, dtype=torch.int64)  # outputs are dim-0 concatenations
+    dist.all_gather_into_tensor(cnts, cnt)                        # (the form gloo accepts as well as NCCL)
+    cnts = cnts.reshape(world, 2).cpu()
     n_all, r_all = cnts[:, 0].tolist(), cnts[:, 1].tolist()
     nmax, rmax, r_tot = max(n_all), max(r_all), sum(r_all)
     empty = dict(min_1=torch.zeros(0, device=dev), R=torch.zeros(0, 3, 3, device=dev),
@@ -292,8 +292,9 @@ def _balanced_retry(srcF, tgtF, p_rows, pair_rows, base_rows, scale_rows, kernel
     # failed pairs of every rank, padded to nmax per rank: global pair index = rank*nmax + local
     clouds = torch.zeros(2, nmax, N, 3, device=dev)
     clouds[0, :n_l], clouds[1, :n_l] = srcF, tgtF
-    g_clouds = torch.empty(world, 2, nmax, N, 3, device=dev)
+    g_clouds = torch.empty(world * 2, nmax, N, 3, device=dev)
     dist.all_gather_into_tensor(g_clouds, clouds)
+    g_clouds = g_clouds.reshape(world, 2, nmax, N, 3)
     g_src = g_clouds[:, 0].reshape(world * nmax, N, 3).contiguous()
     g_tgt = g_clouds[:, 1].reshape(world * nmax, N, 3).contiguous()
     # row descriptions [rmax, 11]: 8 initial values, pair (global), angle_base, gradient scale
@@ -303,8 +304,9 @@ def _balanced_retry(srcF, tgtF, p_rows, pair_rows, base_rows, scale_rows, kernel
         desc[:rows_l, 8] = (torch.cat(pair_rows) + rank * nmax).float()  # < 2^24: exact in float32
         desc[:rows_l, 9] = torch.cat(base_rows).float()
         desc[:rows_l, 10] = torch.cat(scale_rows)
-    g_desc = torch.empty(world, rmax, 11, device=dev)
+    g_desc = torch.empty(world * rmax, 11, device=dev)
     dist.all_gather_into_tensor(g_desc, desc)
+    g_desc = g_desc.reshape(world, rmax, 11)
     rows = torch.cat([g_desc[k, :r_all[k]] for k in range(world)])  # [r_tot, 11], rank-major
     chunk = (r_tot + world - 1) // world
     lo, hi = min(rank * chunk, r_tot), min((rank + 1) * chunk, r_tot)
