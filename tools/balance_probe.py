@@ -14,7 +14,7 @@ P = int(sys.argv[1]) if len(sys.argv) > 1 else 150
 s, t, _ = synth.make_pairs(rank * P, P)
 src, tgt = torch.from_numpy(s).cuda(), torch.from_numpy(t).cuda()
 res = {}
-for balance in (False, True, False, True):
+for balance in (False, True):
     dist.barrier(); torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
