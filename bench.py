@@ -2,7 +2,7 @@
 """Contract benchmark: registered pairs/sec for full HOUV registration
 (BASELINE.json metric) on N B200s of one node.
 
-    python bench.py [--gpus N --steps K --warmup W] [--impl reference]
+    python bench.py [--gpus N --steps K --warmup W] [--impl reference] [--no-balance]
     torchrun ... bench.py --gpus N ...          (one rank per GPU, NCCL)
 
 A "step" registers this rank's shard of the synthetic MVP-shaped set with
