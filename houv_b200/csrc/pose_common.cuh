@@ -35,7 +35,15 @@ struct PoseArgs {
     double *params64, *adam_m64, *adam_v64;
     float *tran_s_out;  // [rows] |T| of the last forward, or null
     const float *row_scale;  // [rows] per-row grad_scale, or null (= grad_scale)
+    // one-row kernels only: skip every row that pose_duo_kernel took (rows 2b, 2b+1 of one pair)
+    int only_unpaired;
 };
+
+__device__ __forceinline__ bool row_is_paired(const PoseArgs &A, int row) {
+    const int other = row ^ 1;
+    if (other >= A.rows) return false;
+    return A.row_pair ? A.row_pair[row] == A.row_pair[other] : row / A.K == other / A.K;
+}
 
 // squared distance of metric m between (tx,ty,tz) and (qx,qy,qz), scalar, same
 // arithmetic as the packed scan (and as the reference on masked clouds)
@@ -218,5 +226,6 @@ __device__ __forceinline__ void state_store(const PoseState &st, const PoseArgs 
 }
 
 int launch_pose_sym(const PoseArgs &a, int unroll, cudaStream_t st);  // pose_sym.cu
+int launch_pose_duo(const PoseArgs &a, cudaStream_t st);              // pose_duo.cu
 
 }  // namespace houv

@@ -84,3 +84,24 @@ def make_pairs(first, count, n_points=2048, **kw):
     """Pairs [first, first+count): src[count,n,3], tgt[count,n,3], transform[count,4,4]."""
     out = [make_pair(first + i, n_points, **kw) for i in range(count)]
     return tuple(np.stack([o[k] for o in out]) for k in range(3))
+
+
+def make_overlap_pair(p, n_points=2048, max_angle=np.pi / 4.5, max_trans=0.5, seed=7000):
+    """A well-conditioned pair for end-state parity checks (SURVEY §7 hard part 1 (iii)): both
+    clouds are different random subsets of the SAME partial view (full overlap, no exact
+    correspondences), relative rotation below `max_angle` (40 deg: inside what angle_base 0 can
+    reach, houv.py:96).  -> src[n,3], tgt[n,3], transform[4,4] (float32), deterministic in p."""
+    rng = np.random.RandomState(seed + p)
+    full = _surface(rng, 8 * n_points)
+    d = rng.randn(3)
+    d /= np.linalg.norm(d)
+    keep = np.argsort(-(full @ d))[: int(len(full) * 0.6)]
+    part1 = full[rng.choice(keep, n_points, replace=False)]
+    part2 = full[rng.choice(keep, n_points, replace=False)]
+    transform, _ = random_pose(rng, max_angle, max_trans / 2)
+    pose1, _ = random_pose(rng, np.pi, max_trans)
+    pose2 = transform @ pose1
+    src = part1 @ pose1[:3, :3].T + pose1[:3, 3]
+    tgt = part2 @ pose2[:3, :3].T + pose2[:3, 3]
+    f = np.float32
+    return src.astype(f), tgt.astype(f), transform.astype(f)

@@ -254,7 +254,72 @@ def make_idam():
     print("idam fixtures written")
 
 
-FAMILIES = {"idam": make_idam, "chamfer": make_chamfer, "houv": make_houv, "svd": make_svd, "solve": make_solve, "calccd": make_calccd}
+def make_houv_full(n_easy=2, hard=(3,), tag="houv_full"):
+    """houv_full.npz: the reference's OWN solve_model / predict_model (houv.py:106-206, loaded
+    unmodified) at BASELINE config 4's shape -- 2048 points x 64 starts x 200 iterations -- on
+    `n_easy` well-conditioned pairs (synth.make_overlap_pair) and the synth.make_pair pairs in
+    `hard` (partial overlap; whichever of them ends above 0.030 takes the reference through its
+    retry cascade at angle_base 1..3).  metrics.cd is served by the thread-parallel C restatement,
+    re-checked against the reference kernel source every 40th call (ref_loader.FAST_CD).
+    Recorded by wrapping (not editing) the module's Predict_loss / predict_model names:
+      pm{c}_base, pm{c}_npairs           which predict_model call (c = 0: all pairs, base 0;
+                                          c = 1..3: the retry sub-batch at angle_base c)
+      pm{c}_trace[its, rows] float32     min_1 of every forward (houv.py:123)
+      pm{c}_loss[its, rows]              6*min_1 + views of every forward
+      pm{c}_min1[B,K], pm{c}_R, pm{c}_T  what predict_model returned (:134-138)
+      ans, r_err, t_err, mse             solve_model's result and the three metrics."""
+    import time
+    import torch
+    import ref_loader
+    from houv_b200 import synth
+    from oracle import chamfer as oc
+    oc.set_threads(os.cpu_count() or 8)
+    ref_loader.FAST_CD = True
+    m = ref_loader.load()
+    H, tu = m["houv"], m["tu"]
+    pairs = [synth.make_overlap_pair(i) for i in range(n_easy)] + [synth.make_pair(p) for p in hard]
+    s, t, tr = (np.stack([q[k] for q in pairs]) for k in range(3))
+    src, tgt, gt = torch.from_numpy(s), torch.from_numpy(t), torch.from_numpy(tr)
+    out = dict(src=s, tgt=t, transform=tr)
+    calls, cur = [], {}
+    pl, pm = H.Predict_loss, H.predict_model
+
+    def rec_loss(a, b, *k, **kw):
+        loss, min_1 = pl(a, b, *k, **kw)
+        cur["trace"].append(min_1.detach().numpy().copy())
+        cur["loss"].append(loss.detach().numpy().copy())
+        return loss, min_1
+
+    def rec_pm(net, a, b, *k, **kw):
+        cur.clear()
+        cur.update(trace=[], loss=[], base=kw.get("angle_base", 0), npairs=a.shape[0])
+        t0 = time.time()
+        l, R, T = pm(net, a, b, *k, **kw)
+        print("  predict_model base %d, %d pairs: %.0f s" % (cur["base"], a.shape[0], time.time() - t0),
+              flush=True)
+        calls.append(dict(cur, min1=l.detach().numpy().copy(), R=R.detach().numpy().copy(),
+                          T=T.detach().numpy().copy()))
+        return l, R, T
+
+    H.Predict_loss, H.predict_model = rec_loss, rec_pm
+    try:
+        r_err, t_err, ans = H.solve_model(H.HOUV(64, 0), src, tgt, gt, kernel=64, num_epochs=200)
+    finally:
+        H.Predict_loss, H.predict_model = pl, pm
+    for c, d in enumerate(calls):
+        out["pm%d_base" % c], out["pm%d_npairs" % c] = np.int32(d["base"]), np.int32(d["npairs"])
+        out["pm%d_trace" % c] = np.stack(d["trace"]).astype(np.float32)
+        out["pm%d_loss" % c] = np.stack(d["loss"]).astype(np.float32)
+        out["pm%d_min1" % c], out["pm%d_R" % c], out["pm%d_T" % c] = d["min1"], d["R"], d["T"]
+    out.update(n_calls=np.int32(len(calls)), ans=ans.detach().numpy(), r_err=r_err.detach().numpy(),
+               t_err=t_err.detach().numpy(), mse=tu.rmse_loss(src, ans.detach(), gt).numpy())
+    np.savez_compressed(os.path.join(HERE, tag + ".npz"), **out)
+    print(tag, "written: r_err", out["r_err"], "t_err", out["t_err"], "calls", len(calls))
+
+
+FAMILIES = {"houv_full": make_houv_full,
+            "houv_full_retry": lambda: make_houv_full(0, (6, 26, 30), "houv_full_retry"),
+            "idam": make_idam, "chamfer": make_chamfer, "houv": make_houv, "svd": make_svd, "solve": make_solve, "calccd": make_calccd}
 
 if __name__ == "__main__":
     want = sys.argv[1:] or list(FAMILIES)

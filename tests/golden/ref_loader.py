@@ -30,6 +30,9 @@ REF = "/root/reference"
 REG = os.path.join(REF, "registration")
 
 _loaded = {}
+FAST_CD = False      # serve metrics.cd from oracle/_build (threads + AVX2) instead of oracle/_ref
+FAST_CD_CHECK = 40   # ... and compare with oracle/_ref every so many calls
+_calls = [0]
 
 
 class _RefChamferFunction(torch.autograd.Function):
@@ -39,7 +42,19 @@ class _RefChamferFunction(torch.autograd.Function):
     @staticmethod
     def forward(ctx, xyz1, xyz2):
         from oracle import chamfer as oc
-        d1, d2, i1, i2 = oc.ref_chamfer_forward(xyz1.detach().numpy(), xyz2.detach().numpy())
+        x1, x2 = xyz1.detach().numpy(), xyz2.detach().numpy()
+        if FAST_CD:
+            # full-size goldens: the thread-parallel C restatement (bit-equal to the reference
+            # kernel source, tests/test_oracle_cpu.py), re-checked here against oracle/_ref on
+            # the first rows of every FAST_CD_CHECK-th call
+            d1, d2, i1, i2 = oc.chamfer_forward(x1, x2)
+            _calls[0] += 1
+            if _calls[0] % FAST_CD_CHECK == 1:
+                r = oc.ref_chamfer_forward(x1[:2], x2[:2])
+                for a, b in zip((d1, d2, i1, i2), r):
+                    assert np.array_equal(a[:2], b, equal_nan=True), "C oracle != reference kernel"
+        else:
+            d1, d2, i1, i2 = oc.ref_chamfer_forward(x1, x2)
         dist1, dist2 = torch.from_numpy(d1), torch.from_numpy(d2)
         idx1, idx2 = torch.from_numpy(i1), torch.from_numpy(i2)
         ctx.save_for_backward(xyz1, xyz2, idx1, idx2)

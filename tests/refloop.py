@@ -1,0 +1,54 @@
+"""TEST INFRASTRUCTURE: the reference's predict_model loop as the reference runs it on a GPU
+(houv.py:106-138: torch HOUV.forward, Predict_loss = 4 chamfer calls + 8 top-k, autograd backward,
+torch.optim.Adam) over the reference's OWN CUDA extension built unmodified for sm_100a
+(oracle/_ref/chamfer_3D.so through oracle/ref_ext.py).  The reference's python files cannot be
+imported on the GPU box (/root/reference is absent there), so the loop body is the restated
+HOUV.forward / Predict_loss of houv_b200 (pinned to the reference's files by houv_ref.npz on the CPU
+side) with `cd` swapped for the reference extension -- none of our kernels run in it."""
+import torch
+from torch.autograd import Function
+
+
+def reference_predict_model(src, tgt, kernel=64, num_epochs=200, angle_base=0):
+    """src, tgt [B,N,3] CUDA -> min_1[B,K], R[B,K,3,3], T[B,K,3] of the last forward."""
+    from houv_b200 import loss as L, solver
+    from oracle import ref_ext
+    ref = ref_ext.load()
+
+    class RefFn(Function):  # dist_chamfer_3D.py:26-64
+        @staticmethod
+        def forward(ctx, xyz1, xyz2):
+            d1, d2, i1, i2 = ref_ext.chamfer_forward(xyz1, xyz2)
+            ctx.save_for_backward(xyz1, xyz2, i1, i2)
+            return d1, d2, i1, i2
+
+        @staticmethod
+        def backward(ctx, g1, g2, gi1, gi2):
+            xyz1, xyz2, i1, i2 = ctx.saved_tensors
+            gx1, gx2 = torch.zeros_like(xyz1), torch.zeros_like(xyz2)
+            ref.backward(xyz1, xyz2, gx1, gx2, g1.contiguous(), g2.contiguous(), i1, i2)
+            return gx1, gx2
+
+    class RefCd(torch.nn.Module):
+        def forward(self, a, b):
+            return RefFn.apply(a.contiguous(), b.contiguous())
+
+    B, N, _ = src.shape
+    s = src.unsqueeze(1).expand(-1, kernel, -1, -1).reshape(-1, N, 3)
+    t = tgt.unsqueeze(1).expand(-1, kernel, -1, -1).reshape(-1, N, 3)
+    old = L.cd
+    L.cd = RefCd
+    try:
+        net = solver.HOUV(B * kernel, angle_base)
+        net.reset_weight(B * kernel, angle_base)
+        opt = torch.optim.Adam(net.parameters(), lr=0.01)
+        for _ in range(num_epochs):
+            opt.zero_grad()
+            src_temp, R, T = net(s)
+            rmse, min_1 = L.Predict_loss(src_temp, t)
+            rmse.mean().backward()
+            opt.step()
+    finally:
+        L.cd = old
+    return (min_1.detach().reshape(B, kernel), R.detach().reshape(B, kernel, 3, 3),
+            T.detach().reshape(B, kernel, 3))

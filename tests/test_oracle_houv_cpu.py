@@ -136,3 +136,19 @@ def test_idam_step_restatement_matches_reference_golden():
             got = oh.idam_step(k("src"), tgt, k("corr"), k("logits"), k("Rin"), k("tin"))
             for name, v in zip(("out", "R", "t", "Rab", "tab", "w"), got):
                 assert torch.allclose(v, k(name), atol=1e-6), (tag, it, name)
+
+
+def test_oracle_follows_reference_at_full_size():
+    """houv_full.npz: the reference's own predict_model at BASELINE config 4's shape (2048 points x
+    64 starts, 3 pairs).  The restated oracle must follow its min_1 / loss traces over the first
+    iterations at the same size (the whole 200-iteration horizon is the GPU test's job)."""
+    from oracle import chamfer as oc
+    import os
+    oc.set_threads(os.cpu_count() or 8)
+    g = load_npz("houv_full.npz")
+    src, tgt = torch.from_numpy(g["src"]), torch.from_numpy(g["tgt"])
+    trace = []
+    oh.predict_model(oh.HOUV(), src, tgt, kernel=64, num_epochs=4, angle_base=0, trace=trace)
+    for k in range(4):
+        assert _close(trace[k]["min_1"], g["pm0_trace"][k], 1e-5)
+        assert _close(trace[k]["loss"], g["pm0_loss"][k], 1e-5)

@@ -23,10 +23,11 @@ N_SMALL = 256
 KERNEL = 32
 
 
-@pytest.fixture(autouse=True, params=[13, 0], ids=["k3-symmetric", "k3-two-scans"])
+@pytest.fixture(autouse=True, params=[20, 13, 0], ids=["k3-duo", "k3-symmetric", "k3-two-scans"])
 def pose_variant(request):
-    """Every test of this module runs against both K3 kernels: the symmetric scan
-    (csrc/pose_sym.cu, the default) and the two-directed-scans kernel (csrc/pose_opt.cu)."""
+    """Every test of this module runs against all K3 kernels: two rows of a pair per CTA
+    (csrc/pose_duo.cu, the default), the symmetric scan with one row per CTA (csrc/pose_sym.cu)
+    and the two-directed-scans kernel (csrc/pose_opt.cu)."""
     from houv_b200 import _lib
     lib = _lib.load()
     lib.houv_set_pose_variant(request.param)
@@ -217,3 +218,60 @@ def test_equality_argmin_recovery_equals_distance_index_search(pose_variant, n, 
     for other in res[1:]:
         for a, b in zip(res[0], other):
             assert torch.equal(a, b)
+
+
+@pytest.mark.parametrize("n,iters,pairs", [(2048, 4, 3), (256, 7, 2), (333, 5, 2), (1000, 3, 1),
+                                           (64, 4, 1), (1100, 3, 2)])
+def test_duo_equals_single_row_kernel(pose_variant, n, iters, pairs):
+    """pose_duo_kernel (two rows of a pair per CTA, 256 threads per row, one team sweeping all
+    superblocks) takes every floating-point sum in pose_sym_kernel's order: trace, outputs,
+    parameters and both Adam moments identical bit for bit -- also with exact ties, with a cloud
+    size that is no multiple of 64 / 256, and resumed from a state."""
+    if pose_variant != 20:
+        pytest.skip("compares the two-row kernel with the one-row kernel")
+    from houv_b200 import _lib, solver
+    lib = _lib.load()
+    src, tgt, _ = _pairs(21, pairs, n=n)
+    src[:, 5] = src[:, 4]
+    tgt[:, n - 1] = tgt[:, 3]
+    res = []
+    for variant in (13, 20):
+        lib.houv_set_pose_variant(variant)
+        out, params, m, v = _gpu_run(src, tgt, iters)
+        more = solver.pose_optimise(src.cuda(), tgt.cuda(), params, KERNEL, 2, adam_m=m, adam_v=v,
+                                    step0=iters, angle_base=2, want_trace=True, want_loss=True)
+        res.append((out["trace"].clone(), out["min_1"].clone(), out["R"].clone(), out["T"].clone(),
+                    out["loss"].clone(), more["trace"].clone(), more["T"].clone(), params.clone(),
+                    m.clone(), v.clone()))
+    lib.houv_set_pose_variant(20)
+    for a, b in zip(*res):
+        assert torch.equal(a, b)
+
+
+def test_duo_row_layouts(pose_variant):
+    """Rows that cannot share a CTA with a partner of the same pair -- an odd row count, neighbours
+    of different pairs in a caller-made row_pair -- are left to the one-row kernel by the same call;
+    per-row angle_base and gradient scale as in solve_model_batches' retry launch."""
+    if pose_variant != 20:
+        pytest.skip("row pairing exists in the two-row kernel only")
+    from houv_b200 import _lib, solver
+    lib = _lib.load()
+    src, tgt, _ = _pairs(31, 3, n=256)
+    g = torch.Generator().manual_seed(5)
+    rows = 37  # odd; pairs change at odd and even positions
+    row_pair = torch.tensor([0] * 5 + [1] * 8 + [2] * 3 + [0] * 4 + [2] * 17, dtype=torch.int32)
+    row_base = torch.randint(0, 4, (rows,), generator=g, dtype=torch.int32)
+    row_scale = (torch.rand(rows, generator=g) + 0.5) / rows
+    init = torch.from_numpy(solver.initial_parameters(64))[:rows].contiguous()
+    res = []
+    for variant in (13, 20):
+        lib.houv_set_pose_variant(variant)
+        params = init.clone().cuda()
+        out = solver.pose_optimise(src.cuda(), tgt.cuda(), params, KERNEL, 5, row_pair=row_pair.cuda(),
+                                   row_base=row_base.cuda(), row_scale=row_scale.cuda(),
+                                   want_trace=True)
+        res.append((out["trace"].clone(), out["min_1"].clone(), out["R"].clone(), out["T"].clone(),
+                    params.clone()))
+    lib.houv_set_pose_variant(20)
+    for a, b in zip(*res):
+        assert torch.equal(a, b)
