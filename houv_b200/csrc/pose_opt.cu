@@ -414,7 +414,7 @@ __global__ void __launch_bounds__(kThreads, 2) pose_kernel(const PoseArgs A) {
 }
 
 static int g_pose_variant = -1;
-constexpr int kDefaultPoseVariant = 13;  // 0..5: two directed scans (this file); 10: symmetric scan (pose_sym.cu)
+constexpr int kDefaultPoseVariant = 20;  // 20: two rows per CTA (pose_duo.cu); 10..17: one row per CTA (pose_sym.cu); 0..5: two directed scans (this file)
 
 template <int kQ, int H, int U>
 static int launch_pose(const PoseArgs &a, cudaStream_t st) {

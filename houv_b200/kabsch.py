@@ -1,9 +1,13 @@
 """Drop-in for the reference's Kabsch head
-(/root/reference/registration/model_utils.py:213-255 `SVDHead`, and its
-duplicates models/idam.py:152-189, models/dcp.py:331-381): same constructor and
-forward signature, R[B,3,3] and t[B,3] out.  The per-sample Python loop of
-torch.svd + torch.det + host-synchronising `if` (:232-240) is ONE launch of the
-warp-per-pair K4 kernel (houv_kabsch)."""
+(/root/reference/registration/model_utils.py:213-255 `SVDHead` and its duplicate
+models/idam.py:152-189): same constructor and forward signature, R[B,3,3] and t[B,3] out.  The
+per-sample Python loop of torch.svd + torch.det + host-synchronising `if` (:232-240) is ONE
+launch of the warp-per-pair K4 kernel (houv_kabsch: one-sided Jacobi SVD of the 3x3 in float64).
+
+FORWARD ONLY.  Both callers on the path detach the result (idam.py:337-338; train_ICP.py never
+differentiates).  DCP's head (models/dcp.py:331-381) has another signature AND is trained by
+back-propagation through torch.svd: it is not claimed, and inputs that require grad raise here
+instead of silently returning R, t without a graph."""
 import torch
 import torch.nn as nn
 
@@ -14,6 +18,11 @@ def kabsch(src, src_corr, weights=None):
     """src, src_corr [B,3,N] float32 CUDA; weights [B,1,N] or [B,N] or None -> R[B,3,3], t[B,3]."""
     _lib.require_cuda_f32(src, "src")
     _lib.require_cuda_f32(src_corr, "src_corr")
+    if torch.is_grad_enabled() and any(x is not None and x.requires_grad
+                                       for x in (src, src_corr, weights)):
+        raise RuntimeError("houv_b200 kabsch / SVDHead is forward-only (no autograd through the "
+                           "SVD): detach the inputs as idam.py:337-338 does, or call it under "
+                           "torch.no_grad()")
     if src.dim() != 3 or src.shape[1] != 3 or src.shape != src_corr.shape:
         raise RuntimeError("src and src_corr must both be [B, 3, N], got %s and %s"
                            % (tuple(src.shape), tuple(src_corr.shape)))

@@ -66,6 +66,44 @@ def _call_report(g, c, src, tgt, kernel=64):
     return rep, m1r
 
 
+def reference_envelope(name="houv_full", alt="houv_full_alt", kernel=64):
+    """The reference against ITSELF: `alt` is the same run of the reference's solve_model with its
+    gradient kernel adding in the opposite point order (the reference uses float atomics, whose
+    order the GPU is free to choose: chamfer3D.cu:166-171, registration/README.md:82-90).  Same
+    statistics as _call_report -- the yardstick for what 'parity' can mean at 200 iterations."""
+    a = np.load(os.path.join(GOLDEN_DIR, name + ".npz"))
+    b = np.load(os.path.join(GOLDEN_DIR, alt + ".npz"))
+    ta, tb = a["pm0_trace"], b["pm0_trace"]
+    rel = np.abs(tb - ta) / np.maximum(np.abs(ta), 1e-30)
+    rep = dict(fixtures=[name + ".npz", alt + ".npz"], checkpoints={})
+    for k in CHECKPOINTS:
+        r = rel[k - 1]
+        rep["checkpoints"][str(k)] = dict(
+            max_rel=float(r.max()), median_rel=float(np.median(r)),
+            frac_within_1e_5=float((r <= 1e-5).mean()), frac_within_1e_4=float((r <= 1e-4).mean()),
+            frac_within_1e_3=float((r <= 1e-3).mean()))
+    rows = ta.shape[1]
+    npairs = rows // kernel
+    Ra, Rb = a["pm0_R"].reshape(rows, 3, 3), b["pm0_R"].reshape(rows, 3, 3)
+    Ta, Tb = a["pm0_T"].reshape(rows, 3), b["pm0_T"].reshape(rows, 3)
+    dr, dt = _rot_delta_rad(Ra, Rb), np.linalg.norm(Ta - Tb, axis=1)
+    rep["end_state_all_starts"] = dict(
+        rot_rad_median=float(np.median(dr)), rot_rad_max=float(dr.max()),
+        trans_median=float(np.median(dt)), trans_max=float(dt.max()),
+        frac_within_bar=float(((dr <= 1e-4) & (dt <= 1e-5)).mean()))
+    sa, sb = a["pm0_min1"].argmin(1), b["pm0_min1"].argmin(1)
+    idx = np.arange(npairs)
+    rep["selected"] = dict(
+        same_start=[bool(x == y) for x, y in zip(sa, sb)],
+        rot_rad=[float(x) for x in _rot_delta_rad(a["pm0_R"][idx, sa], b["pm0_R"][idx, sb])],
+        trans=[float(x) for x in np.linalg.norm(a["pm0_T"][idx, sa] - b["pm0_T"][idx, sb], axis=1)],
+        best_min_1_rel=[float(abs(x - y) / x) for x, y in zip(a["pm0_min1"][idx, sa],
+                                                              b["pm0_min1"][idx, sb])])
+    rep["metrics"] = dict(r_err_deg=[[float(x) for x in a["r_err"]], [float(x) for x in b["r_err"]]],
+                          t_err=[[float(x) for x in a["t_err"]], [float(x) for x in b["t_err"]]])
+    return rep
+
+
 def full_parity_report(name="houv_full", calls=None):
     """-> dict: per predict_model call the trace deviations at CHECKPOINTS, end states, selected
     starts; and solve_model's ans / metrics against the reference's."""
@@ -94,4 +132,6 @@ def full_parity_report(name="houv_full", calls=None):
         r_err_deg=[float(x) for x in r_err.cpu()], r_err_deg_ref=[float(x) for x in g["r_err"]],
         t_err=[float(x) for x in t_err.cpu()], t_err_ref=[float(x) for x in g["t_err"]],
         bottom_row_zero=bool((a[:, 3] == 0).all()))
+    if os.path.exists(os.path.join(GOLDEN_DIR, name + "_alt.npz")):
+        rep["reference_against_itself"] = reference_envelope(name, name + "_alt")
     return rep

@@ -11,7 +11,7 @@ train_HOUV.py:69,100-112): each rank walks its range in batches and calls
 solve_model per batch.  A pair's result depends on the batch it sits in
 (initial values are drawn per batch row, houv.py:116, and the loss is the mean
 over the batch, :124), so results are independent of the number of GPUs exactly
-when `batch_size` divides the per-rank range -- the launcher checks that.
+when `batch_size` divides the per-rank range -- `check_layout` says so (bench.py prints it).
 """
 import os
 
@@ -81,16 +81,45 @@ def register_pairs(src, tgt, transform=None, batch_size=50, kernel=64, num_epoch
 
 def gather_results(ans, metrics, world):
     """The only collective of the path: all_gather of [P_local, 16+3] floats
-    (NCCL over NVLink on GPUs, gloo in the CPU tests).  Ranks hold equal counts."""
+    (NCCL over NVLink on GPUs, gloo in the CPU tests).  Ranks may hold DIFFERENT counts
+    (shard_range gives 3,3,3,1 for 10 pairs on 4 ranks, or none at all): the per-rank counts are
+    gathered first, every rank pads to the largest, and the padding is dropped after the
+    gather -- rows come back in rank order = pair order."""
     packed = torch.cat([ans.reshape(ans.shape[0], 16),
                         metrics if metrics is not None else ans.new_zeros(ans.shape[0], 3)], dim=1)
     packed = packed.contiguous()
     if world > 1:
-        out = packed.new_empty(world * packed.shape[0], packed.shape[1])
-        torch.distributed.all_gather_into_tensor(out, packed)
+        dist = torch.distributed
+        n_l = packed.shape[0]
+        cnt = torch.tensor([n_l], device=packed.device, dtype=torch.int64)
+        cnts = torch.empty(world, device=packed.device, dtype=torch.int64)
+        dist.all_gather_into_tensor(cnts, cnt)
+        counts = cnts.tolist()
+        nmax = max(counts)
+        if nmax == 0:
+            out = packed
+        else:
+            padded = packed.new_zeros(nmax, packed.shape[1])
+            padded[:n_l] = packed
+            g = packed.new_empty(world * nmax, packed.shape[1])
+            dist.all_gather_into_tensor(g, padded)
+            g = g.reshape(world, nmax, packed.shape[1])
+            out = torch.cat([g[k, :counts[k]] for k in range(world)])
     else:
         out = packed
     return out[:, :16].reshape(-1, 4, 4), out[:, 16:]
+
+
+def check_layout(total, world, batch_size):
+    """Results are independent of the number of GPUs exactly when every rank's range is a whole
+    number of batches (a pair's result depends on its position in its batch: houv.py:116,124).
+    -> None when that holds, else a one-line warning text (bench.py and examples print it)."""
+    per = (total + world - 1) // world
+    if world > 1 and (per % batch_size != 0 or total % per != 0):
+        return ("%d pairs on %d ranks in batches of %d: per-rank range %d is not a whole number of "
+                "batches (or the last rank is short) -- poses will differ from a 1-GPU run"
+                % (total, world, batch_size, per))
+    return None
 
 
 # ----------------------------------------------------------------- result files

@@ -137,6 +137,9 @@ def pose_optimise(src, tgt, params, kernel, iters, angle_base=0, grad_scale=None
             params.dtype not in (torch.float32, torch.float64):
         raise RuntimeError("params must be a float32 or float64 CUDA tensor "
                            "(houv_b200 has no CPU path)")
+    if iters <= 0:
+        # the reference's loop would leave min_1 / R / T undefined (houv.py:134 NameError)
+        raise RuntimeError("pose_optimise needs iters >= 1 (got %d)" % iters)
     f64 = params.dtype == torch.float64
     src, tgt = src.contiguous(), tgt.contiguous()
     P, N, _ = src.shape

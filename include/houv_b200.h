@@ -47,7 +47,15 @@ const char *houv_version(void);
  * Arithmetic is the reference's, bit for bit: d = fma(dz,dz,fma(dx,dx,dy*dy)),
  * dx = target.x - query.x, strict '<' in ascending j  (chamfer3D.cu:32-36,126).
  * Outputs need not be pre-zeroed.  M == 0 (or N == 0) zero-fills the affected
- * outputs, which is what the reference's zero-initialised buffers end up as. */
+ * outputs, which is what the reference's zero-initialised buffers end up as.
+ * FINITE INPUTS ONLY.  Every finite float32 is handled bit for bit like the reference,
+ * denormals and coordinates whose differences overflow to +inf included
+ * (tests/test_chamfer_gpu.py::test_extreme_finite_inputs).  NaN or +-inf COORDINATES are
+ * unsupported input: the reference's outcome for them depends on where the NaN sits inside its
+ * 512-point tiles (a NaN at tile position 0 blocks that tile, and the first tile for good:
+ * chamfer3D.cu:36,79,121,126 -- restated and pinned in oracle/chamfer_oracle.c,
+ * tests/test_oracle_cpu.py::test_nan_semantics_follow_the_reference_kernel); these kernels skip
+ * NaN distances in every minimum instead and do not reproduce that. */
 int houv_chamfer3d_forward(const float *xyz1, const float *xyz2, int B, int N, int M,
                            float *dist1, float *dist2, int *idx1, int *idx2, void *stream);
 

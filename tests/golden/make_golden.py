@@ -181,6 +181,31 @@ def make_calccd():
     print("calc_cd fixtures written")
 
 
+def make_small():
+    """small_ref.npz: the remaining reference functions of the path that had no fixture --
+    calc_cd_percent_aligned (model_utils_completion.py:103-116) at percent 0.5 and 1, and
+    nearest_neighbor (model_utils.py:33-37, source executed as-is) on [3, points] inputs."""
+    import torch
+    import ref_loader
+    muc = ref_loader.load()["muc"]
+    rng = np.random.RandomState(21)
+    out = {}
+    o = (rng.rand(3, 96, 3) - 0.5).astype(np.float32)
+    g = (rng.rand(3, 96, 3) - 0.5).astype(np.float32)
+    out["al_output"], out["al_gt"] = o, g
+    for tag, pc in (("50", 0.5), ("100", 1)):
+        r = muc.calc_cd_percent_aligned(torch.from_numpy(o), torch.from_numpy(g), percent=pc)
+        for k, v in zip(("cd_p", "cd_t", "idx1", "idx2", "idxx1", "idxx2"), r):
+            out["al%s_%s" % (tag, k)] = v.numpy()
+    nn = ref_loader.load_function("nearest_neighbor")
+    a = (rng.rand(3, 150) - 0.5).astype(np.float32)
+    b = (rng.rand(3, 170) - 0.5).astype(np.float32)
+    d, i = nn(torch.from_numpy(a), torch.from_numpy(b))
+    out.update(nn_src=a, nn_dst=b, nn_dist=d.numpy(), nn_idx=i.numpy())
+    np.savez_compressed(os.path.join(HERE, "small_ref.npz"), **out)
+    print("small fixtures written", d.shape, i.dtype)
+
+
 def make_svd():
     """svdhead_ref.npz: the reference's SVDHead class (model_utils.py:213-255, source read
     and executed as-is) on noisy rigid correspondences, with and without weights, including
@@ -254,7 +279,7 @@ def make_idam():
     print("idam fixtures written")
 
 
-def make_houv_full(n_easy=2, hard=(3,), tag="houv_full"):
+def make_houv_full(n_easy=2, hard=(3,), tag="houv_full", reversed_atomics=False):
     """houv_full.npz: the reference's OWN solve_model / predict_model (houv.py:106-206, loaded
     unmodified) at BASELINE config 4's shape -- 2048 points x 64 starts x 200 iterations -- on
     `n_easy` well-conditioned pairs (synth.make_overlap_pair) and the synth.make_pair pairs in
@@ -275,6 +300,7 @@ def make_houv_full(n_easy=2, hard=(3,), tag="houv_full"):
     from oracle import chamfer as oc
     oc.set_threads(os.cpu_count() or 8)
     ref_loader.FAST_CD = True
+    ref_loader.BACKWARD_REVERSED = reversed_atomics
     m = ref_loader.load()
     H, tu = m["houv"], m["tu"]
     pairs = [synth.make_overlap_pair(i) for i in range(n_easy)] + [synth.make_pair(p) for p in hard]
@@ -317,7 +343,10 @@ def make_houv_full(n_easy=2, hard=(3,), tag="houv_full"):
     print(tag, "written: r_err", out["r_err"], "t_err", out["t_err"], "calls", len(calls))
 
 
-FAMILIES = {"houv_full": make_houv_full,
+FAMILIES = {"small": make_small, "houv_full": make_houv_full,
+            # the same run with the reference kernel's gradient adds in the opposite order: the
+            # reference against ITSELF (ref_loader.BACKWARD_REVERSED)
+            "houv_full_alt": lambda: make_houv_full(tag="houv_full_alt", reversed_atomics=True),
             "houv_full_retry": lambda: make_houv_full(0, (6, 26, 30), "houv_full_retry"),
             "idam": make_idam, "chamfer": make_chamfer, "houv": make_houv, "svd": make_svd, "solve": make_solve, "calccd": make_calccd}
 

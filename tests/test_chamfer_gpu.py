@@ -230,3 +230,27 @@ def test_completion_shape_c5_properties():
     e = oc.chamfer_forward(gt[row:row + 1].cpu().numpy(), out[row:row + 1].cpu().numpy())
     for g, x in zip((d1, d2, i1, i2), e):
         assert np.array_equal(g[row:row + 1].cpu().numpy(), x)
+
+
+@pytest.mark.parametrize("n,m", [(300, 700), (2048, 2048), (64, 1100)])
+def test_extreme_finite_inputs(n, m):
+    """include/houv_b200.h: FINITE INPUTS ONLY (the reference's NaN handling depends on the position
+    of the NaN inside its 512-point tiles, chamfer3D.cu:36,79,121,126; tests/test_oracle_cpu.py
+    pins the oracle to that, the CUDA kernels do not reproduce it).  Everything finite must match
+    bit for bit, also next to the extremes: denormals (no flush to zero anywhere in the forward),
+    +-3e38 whose differences overflow to +inf distances (first index wins among them), exact zeros,
+    and clouds where EVERY distance of a query is +inf."""
+    rng = np.random.RandomState(n + m)
+    x1 = (rng.rand(2, n, 3) - 0.5).astype(np.float32)
+    x2 = (rng.rand(2, m, 3) - 0.5).astype(np.float32)
+    x1[0, 3] = [3e38, -3e38, 3e38]
+    x2[0, 5] = [-3e38, 3e38, -3e38]
+    x2[0, m - 1] = [3e38, -3e38, 2.9e38]          # near x1[0,3]: finite differences, d overflows
+    x1[0, 7] = [1e-40, -1e-41, 3e-45]             # denormals
+    x2[0, 9] = [1e-40, -1e-41, 0.0]
+    x2[0, 11] = [2e-40, -1e-41, 3e-45]
+    x1[1, 0] = 0.0
+    x2[1, m // 2] = 0.0
+    x1[1, n - 1] = [3.4e38, 3.4e38, 3.4e38]       # every distance from here is +inf -> idx 0
+    _check_fwd(x1, x2)
+    _check_fwd(x2, x1)

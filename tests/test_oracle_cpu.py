@@ -75,3 +75,56 @@ def test_threads_do_not_change_results():
     oc.set_threads(1)
     for u, v in zip(a, b):
         assert np.array_equal(u, v)
+
+
+def test_nan_semantics_follow_the_reference_kernel():
+    """chamfer3D.cu:36,79,121,126: a NaN distance enters `best` only at position 0 of a 512-point
+    tile (k == 0 || d < best) and then blocks that whole tile; across tiles `result > best` skips a
+    NaN tile but can never leave a NaN first tile.  The C restatement (scalar and AVX2 paths) must
+    reproduce the reference kernel source on NaNs at tile positions 0 / 5 / 512 / 513, a NaN
+    query, and +-inf coordinates.  (The CUDA kernels take finite inputs only: include/houv_b200.h.)"""
+    if not oc.ref_available():
+        import pytest
+        pytest.skip("oracle/_ref not built")
+    rng = np.random.RandomState(5)
+    base1 = rng.rand(1, 40, 3).astype(np.float32)
+    base2 = rng.rand(1, 1100, 3).astype(np.float32)
+    cases = []
+    for pos in (0, 5, 512, 513, 1024):
+        b = base2.copy()
+        b[0, pos, 1] = np.nan
+        cases.append((base1, b))
+    a = base1.copy()
+    a[0, 7, 0] = np.nan
+    cases.append((a, base2))
+    b = base2.copy()
+    b[0, 512] = [np.inf, 0, 0]
+    b[0, 3] = [-np.inf, np.inf, 0]
+    cases.append((base1, b))
+    for simd in (1, 0):
+        oc.oracle_lib().oracle_set_simd(simd)
+        for x1, x2 in cases:
+            got, ref = oc.chamfer_forward(x1, x2), oc.ref_chamfer_forward(x1, x2)
+            for g, r in zip(got, ref):
+                assert np.array_equal(g, r, equal_nan=True)
+    oc.oracle_lib().oracle_set_simd(1)
+    # what the semantics are, spelled out once: NaN at tile position 0 of the FIRST tile poisons
+    # every query; at position 512 it hides the whole second tile; at 5 or 513 only that point
+    b = base2.copy(); b[0, 0, 1] = np.nan
+    d1, _, i1, _ = oc.ref_chamfer_forward(base1, b)
+    assert np.isnan(d1).all() and (i1 == 0).all()
+    b = base2.copy(); b[0, 512, 1] = np.nan
+    _, _, i1, _ = oc.ref_chamfer_forward(base1, b)
+    assert not ((i1 >= 512) & (i1 < 1024)).any()
+
+
+def test_simd_and_scalar_paths_agree():
+    rng = np.random.RandomState(6)
+    x1 = rng.rand(3, 203, 3).astype(np.float32)
+    x2 = (rng.randint(0, 5, (3, 517, 3)) / 4.0).astype(np.float32)  # many ties
+    oc.oracle_lib().oracle_set_simd(0)
+    a = oc.chamfer_forward(x1, x2)
+    oc.oracle_lib().oracle_set_simd(1)
+    b = oc.chamfer_forward(x1, x2)
+    for p, q in zip(a, b):
+        assert np.array_equal(p, q)
