@@ -16,9 +16,17 @@ collective).  Weak scaling: every rank holds --pairs-per-gpu pairs (150 = the
 `e2e`        pairs/s through the public API (shard.register_pairs) from PINNED
              HOST buffers: H2D of the clouds and D2H of poses+metrics inside the
              timed region, every step.
-`roofline`   the dominant kernel (K3 pose_kernel) against the FP32 CUDA-core
+`roofline`   the dominant kernel (K3, pose_duo_kernel) against the FP32 CUDA-core
              peak measured live by an FFMA probe ("bound": "fp32" -- K=3 distance
-             evaluation is neither HBM- nor tensor-bound).
+             evaluation is neither HBM- nor tensor-bound).  `frac` /
+             `achieved` count the FLOP the kernel EXECUTES (13 per undirected four-metric
+             point pair); the directed-pair figure of SURVEY 8(d) is `algorithmic_*`.
+`workload`   rows per step, retry fraction, rows/s per rank: pairs/s follows from them.
+`extra`      the same step on the HARD set (objects twice the size: ~20 % of the pairs go
+             through the retry cascade, like MVP's unrestricted rotations), K1/K2 at
+             BASELINE configs 2 and 5 beside the reference's own CUDA extension, K2 against
+             the measured HBM peak, the ICP baseline (config 3), and -- once, untimed --
+             `parity_checked` against the reference-made full-size fixture.
 `cpu_baseline` / --impl reference: the CPU oracle of the same path (restated
              houv.py over the multi-threaded C chamfer oracle) on the box's host
              cores, on a bounded sample, linearly extrapolated (stated in `sample`).
@@ -113,7 +121,8 @@ def cpu_houv_sample(n_iters, threads):
     """One bounded sample of the reference's path on the host: ONE pair, 64 starts,
     `n_iters` of the 200 Adam iterations at angle_base 0, through the CPU oracle
     (oracle/houv.py restates registration/models/houv.py; its Chamfer kernels are
-    oracle/chamfer_oracle.c on `threads` host threads).  Returns seconds."""
+    oracle/chamfer_oracle.c on `threads` host threads, 8 queries per AVX2 vector where the
+    host has AVX2+FMA).  Returns seconds."""
     import torch
     from houv_b200 import synth
     from oracle import chamfer as oc
@@ -139,15 +148,17 @@ def run_reference(args):
     import torch
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
-    n_it = 40  # ~8 s of host work per step on 16 cores: bounded, but long enough to time steadily
+    n_it = 60  # a bounded sample (seconds of host work per step), long enough to time steadily
     for _ in range(args.warmup):
         cpu_houv_sample(1, cores)
     ts = [cpu_houv_sample(n_it, cores) for _ in range(args.steps)]
     sec = sum(ts) / len(ts)
     val = cpu_pairs_per_s(sec, n_it)
     sample = ("each step = 1 pair x %d starts x %d of %d Adam iterations at angle_base 0 "
-              "(2048x2048 pts, 8 directed NN searches + backward per iteration); pairs/s = "
-              "1/(t_step*%d/%d), retries not added" % (KERNEL, n_it, ITERS, ITERS, n_it))
+              "(2048x2048 pts, 8 directed NN searches + backward per iteration; CPU oracle = "
+              "restated houv.py in torch-CPU over the C chamfer restatement, AVX2, all host "
+              "threads); pairs/s = 1/(t_step*%d/%d), retries not added" %
+              (KERNEL, n_it, ITERS, ITERS, n_it))
     print(json.dumps({
         "impl": "reference", "metric": "registered pairs/sec (2048-pt, HOUV full)",
         "value": val, "unit": "pairs/s", "n_gpus": args.gpus, "steps": args.steps,
@@ -174,12 +185,47 @@ def workload_config(args):
 
 
 # ----------------------------------------------------------------- GPU arm
-def chamfer_nn_lines(dev, flush, fp32_peak):
-    """chamfer_3DDist forward at BASELINE configs C2 / C5 and at the HOUV batch shape
-    (6400 rows = 100 pairs x 64 starts): Gpts^2/s = 2*B*N*M / t / 1e9, 8 FLOP per directed
-    point pair against the FP32 peak.  CUDA events, L2 flushed between iterations."""
+def _median_ms(fn, flush, n=8, skip=3):
+    import torch
+    ts = []
+    for i in range(n):
+        flush.add_(1.0)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        fn()
+        e1.record()
+        torch.cuda.synchronize()
+        if i >= skip:
+            ts.append(e0.elapsed_time(e1))
+    return statistics.median(ts)
+
+
+def measured_hbm_peak():
+    """GB/s from MEASURED_PEAKS.json (driver-written, this pool's B200s), else the profiling
+    recipe's fallback."""
+    try:
+        return float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"]), \
+            "MEASURED_PEAKS.json hbm_gbs"
+    except Exception:
+        return 6550.0, "B200_PROFILING.md fallback (MEASURED_PEAKS.json absent)"
+
+
+def chamfer_operator_lines(dev, flush, fp32_peak):
+    """The operator on its own (second half of BASELINE.json's metric): chamfer_3DDist forward at
+    BASELINE configs C2 / C5 and at the HOUV batch shape -- Gpts^2/s = 2*B*N*M / t / 1e9, 8 FLOP
+    per directed point pair against the FP32 peak -- and forward + backward (K1 + K2, graddist =
+    1/N) beside the REFERENCE'S OWN CUDA extension built unmodified for sm_100a
+    (oracle/_ref/chamfer_3D.so; an extra leg like cpu_baseline: never on the product path), same
+    process, same inputs.  K2 alone against the measured HBM peak: 32 B of algorithmic traffic per
+    point (12 xyz + 4 idx + 4 graddist + 12 grad).  CUDA events, L2 flushed between iterations."""
     import torch
     from houv_b200.chamfer import chamfer_3D
+    try:
+        from oracle import ref_ext
+        ref = ref_ext.load() if ref_ext.available() else None
+    except Exception:
+        ref = None
+    hbm, hbm_src = measured_hbm_peak()
     out = {}
     for name, (B, N, M) in (("C2_b32_2048x2048", (32, 2048, 2048)),
                             ("C5_b64_16384x2048", (64, 16384, 2048)),
@@ -190,22 +236,83 @@ def chamfer_nn_lines(dev, flush, fp32_peak):
         d1 = torch.empty(B, N, device=dev); d2 = torch.empty(B, M, device=dev)
         i1 = torch.empty(B, N, device=dev, dtype=torch.int32)
         i2 = torch.empty(B, M, device=dev, dtype=torch.int32)
-        ts = []
-        for i in range(8):
-            flush.add_(1.0)
-            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            e0.record()
+        gd1 = torch.full((B, N), 1.0 / N, device=dev); gd2 = torch.full((B, M), 1.0 / M, device=dev)
+        g1 = torch.empty(B, N, 3, device=dev); g2 = torch.empty(B, M, 3, device=dev)
+
+        def fwd():
             chamfer_3D.forward(x1, x2, d1, d2, i1, i2)
-            e1.record()
-            torch.cuda.synchronize()
-            if i >= 3:
-                ts.append(e0.elapsed_time(e1))
-        ms = statistics.median(ts)
+
+        def bwd():  # what our autograd wrapper calls: assign form, no zero-fill needed
+            chamfer_3D.backward(x1, x2, g1, g2, gd1, gd2, i1, i2, assign=True)
+
+        def both():
+            fwd(); bwd()
+        ms = _median_ms(fwd, flush)
+        ms_b = _median_ms(bwd, flush)
+        ms_fb = _median_ms(both, flush)
         pairs = 2.0 * B * N * M
-        out[name] = {"ms": ms, "Gpts2_per_s": pairs / ms / 1e6,
-                     "frac_fp32_peak": 8.0 * pairs / ms / 1e9 / fp32_peak}
-        del x1, x2, d1, d2, i1, i2
+        k2_bytes = 32.0 * B * (N + M)
+        e = {"ms": ms, "Gpts2_per_s": pairs / ms / 1e6,
+             "frac_fp32_peak": 8.0 * pairs / ms / 1e9 / fp32_peak,
+             "fwd_bwd_ms": ms_fb,
+             "k2_backward": {"ms": ms_b, "algorithmic_bytes": k2_bytes,
+                             "achieved_GBps": k2_bytes / ms_b / 1e6, "peak_GBps": hbm,
+                             "frac_hbm_peak": k2_bytes / ms_b / 1e6 / hbm, "peak_source": hbm_src}}
+        if ref is not None:
+            def ref_both():  # dist_chamfer_3D.py:28-64 with the buffers made on the device
+                z = [torch.zeros(B, N, device=dev), torch.zeros(B, M, device=dev),
+                     torch.zeros(B, N, device=dev, dtype=torch.int32),
+                     torch.zeros(B, M, device=dev, dtype=torch.int32)]
+                ref.forward(x1, x2, *z)
+                a, b = torch.zeros_like(x1), torch.zeros_like(x2)
+                ref.backward(x1, x2, a, b, gd1, gd2, z[2], z[3])
+            r = _median_ms(ref_both, flush, n=5, skip=2)
+            e["reference_ext_fwd_bwd_ms"] = r
+            e["speedup_vs_reference_ext_fwd_bwd"] = r / ms_fb
+        out[name] = e
+        del x1, x2, d1, d2, i1, i2, gd1, gd2, g1, g2
     return out
+
+
+def icp_line(dev, flush):
+    """BASELINE config 3: the ICP block of train_ICP.py:124-190 over 1200 synthetic pairs (2048
+    points, threshold 0.02, <= 500 iterations) -- one launch of houv_icp.  Parity of this path is
+    UNPINNED (Open3D 0.9.0 is absent: DESIGN.md section 2)."""
+    import numpy as np
+    import torch
+    from concurrent.futures import ThreadPoolExecutor
+    from houv_b200 import icp, synth
+    with ThreadPoolExecutor(8) as ex:
+        parts = list(ex.map(lambda p: synth.make_pair(p, N_POINTS), range(1200)))
+    src, tgt, gt = (torch.from_numpy(np.stack([q[k] for q in parts])).to(dev) for k in range(3))
+    ms = _median_ms(lambda: icp.icp_batch(src, tgt, gt), flush, n=5, skip=2)
+    reg = icp.registration_icp(src, tgt, icp.THRESHOLD, icp.TRANS_INIT, icp.MAX_ITERATION)
+    it = reg.iterations.float()
+    return {"workload": "C3: point-to-point ICP, 1200 pairs x 2048 pts, gate 0.02, <= 500 its",
+            "ms": ms, "pairs_per_s": 1200.0 / ms * 1e3, "iterations_mean": float(it.mean()),
+            "iterations_max": float(it.max()),
+            # one CTA per pair, resident for all its iterations: the launch lasts as long as its
+            # longest pair while the mean pair needs iterations_mean
+            "longest_pair_iterations_over_mean": float(it.max() / it.mean()),
+            "parity": "unpinned (Open3D 0.9.0 unavailable on this box)"}
+
+
+def parity_summary():
+    """Once, outside every timed region: K3 / solve_model at the full BASELINE shape against the
+    fixture made by the reference's own solve_model (houv_b200/parity.py)."""
+    from houv_b200 import parity
+    r = parity.full_parity_report("houv_full")
+    c = r["calls"][0]
+    env = r.get("reference_against_itself", {})
+    return {"fixture": r["fixture"], "shape": r["shape"],
+            "min_1_trace_max_rel": {k: v["max_rel"] for k, v in c["checkpoints"].items()},
+            "min_1_trace_median_rel": {k: v["median_rel"] for k, v in c["checkpoints"].items()},
+            "reference_against_itself_median_rel":
+                {k: v["median_rel"] for k, v in env.get("checkpoints", {}).items()},
+            "selected_pose_rot_rad": c["selected"]["rot_rad"], "selected_pose_trans": c["selected"]["trans"],
+            "reference_against_itself_selected_rot_rad": env.get("selected", {}).get("rot_rad"),
+            "solve_model_r_err_deg": r["solve_model"]["r_err_deg"],
+            "solve_model_r_err_deg_ref": r["solve_model"]["r_err_deg_ref"]}
 
 
 def run_ours(args):
@@ -237,6 +344,9 @@ def run_ours(args):
     flush = torch.zeros(64 * 1024 * 1024, device=dev)  # 256 MB > 126 MB L2
 
     balance = world > 1 and not args.no_balance  # retry rows of all ranks dealt evenly (solver._balanced_retry)
+    msg = shard.check_layout(P * world, world, BATCH)
+    if msg and rank == 0:
+        sys.stderr.write("bench.py: " + msg + "\n")
 
     def step_device():
         ans, met = shard.register_pairs(d_src, d_tgt, d_gt, batch_size=BATCH, kernel=KERNEL,
@@ -310,6 +420,49 @@ def run_ours(args):
     ms_e2e, _ = timed(step_e2e, args.steps)
     clocks = sampler.stop() if rank == 0 else None
 
+    def rank_stats(ms_total, steps):
+        """[world, 4] = pairs retried, rows this rank ran per step, this rank's K3 ms per step"""
+        st = solver.LAST_STATS
+        ran = sum(r for _, _, r, _, _ in ktim) / max(steps, 1)
+        kms_r = sum(a.elapsed_time(b) for a, b, *_ in ktim) / max(steps, 1)
+        v = torch.tensor([st.get("retried_pairs", 0), ran, kms_r, st.get("pairs", 0)],
+                         device=dev, dtype=torch.float64)
+        if world > 1:
+            g = torch.empty(world * 4, device=dev, dtype=torch.float64)
+            torch.distributed.all_gather_into_tensor(g, v)
+            return g.reshape(world, 4).cpu().numpy()
+        return v.reshape(1, 4).cpu().numpy()
+    rstats = rank_stats(ms_dev, args.steps)
+
+    # ---- the same step on the HARD set (untimed warm-up + one timed step): objects of twice the
+    # size, so that a wrong-basin pose ends above the 0.030 threshold and ~20 % of the pairs take
+    # the retry cascade, the rate MVP's unrestricted rotations produce (registration/README.md:56-57)
+    hs, ht, htr = synth.make_pairs(first, P, n_points=N_POINTS, radius=1.0)
+    x_src, x_tgt, x_gt = (torch.from_numpy(a).to(dev) for a in (hs, ht, htr))
+
+    def step_hard():
+        ans, met = shard.register_pairs(x_src, x_tgt, x_gt, batch_size=BATCH, kernel=KERNEL,
+                                        num_epochs=args.iters, balance=balance)
+        return shard.gather_results(ans, met, world)
+    step_hard()
+    ktim_main = ktim
+    solver.KERNEL_TIMING = ktim = []
+    ms_hard, (_, met_hard) = timed(step_hard, 1)
+    solver.KERNEL_TIMING = None
+    hstats = rank_stats(ms_hard, 1)
+    ktim = ktim_main
+
+    # ---- N > 1, once, untimed: the balanced retry launch gives the poses of the exchange-free form
+    balance_identical = None
+    if world > 1 and balance:
+        a1, _ = shard.register_pairs(x_src, x_tgt, None, batch_size=BATCH, kernel=KERNEL,
+                                     num_epochs=args.iters, balance=True)
+        a0, _ = shard.register_pairs(x_src, x_tgt, None, batch_size=BATCH, kernel=KERNEL,
+                                     num_epochs=args.iters, balance=False)
+        same = torch.tensor([1.0 if torch.equal(a0, a1) else 0.0], device=dev)
+        torch.distributed.all_reduce(same, op=torch.distributed.ReduceOp.MIN)
+        balance_identical = bool(same.item() == 1.0)
+
     # dominant kernel (K3, symmetric scan).  Algorithmic work (SURVEY 8d): 13 FLOP per directed
     # four-metric point pair, 2*N*M directed pairs per row-iteration = 26*N*M.  The symmetric
     # kernel evaluates d(i,j) once for both directions, so it EXECUTES 13*N*M; the reference's
@@ -323,14 +476,37 @@ def run_ours(args):
     value = total_pairs / (ms_dev / 1e3)
     e2e = total_pairs / (ms_e2e / 1e3)
     met = met.float().cpu().numpy()
-    traffic = None
+    met_hard = met_hard.float().cpu().numpy()
+    traffic, traffic_src = None, None
     tfile = os.path.join(ROOT, "profiles", "k3_traffic.json")
     if os.path.exists(tfile):
-        # ncu capture (one launch of 320 rows) scaled to this run's average rows per launch:
-        # the kernel reads each pair's two clouds once per row and nothing else from HBM
-        per_row = json.load(open(tfile)).get("dram_bytes_per_row")
+        # NOT a measurement of this launch: one ncu --set full capture of a small launch, scaled to
+        # this run's average rows per launch (the kernel reads each pair's two clouds once per row
+        # and nothing else from HBM; compute-bound by four orders of magnitude either way)
+        tj = json.load(open(tfile))
+        per_row = tj.get("dram_bytes_per_row")
         if per_row and ktim:
             traffic = per_row * sum(r for _, _, r, _, _ in ktim) / len(ktim)
+            traffic_src = "scaled by rows from a %s-row ncu capture (%s)" % (
+                tj.get("rows", "small"), tj.get("source", "profiles/k3_traffic.json"))
+
+    def workload_stats(rs, ms_total, steps, pairs_per_rank):
+        rows_rank = rs[:, 1]                       # rows each rank ran per step
+        retried = float(rs[:, 0].sum())
+        step_s = ms_total / steps / 1e3
+        return {"pairs_per_step": int(pairs_per_rank * world),
+                "retried_pairs_per_step": int(retried),
+                "retry_fraction": retried / (pairs_per_rank * world),
+                "rows_per_step": float(rows_rank.sum()),
+                "rows_per_step_per_rank_max": float(rows_rank.max()),
+                "rows_per_step_per_rank_mean": float(rows_rank.mean()),
+                # rows/s of a rank over the step, and over its K3 launches alone
+                "rows_per_s_per_rank_mean": float(rows_rank.mean() / step_s),
+                "rows_per_s_per_rank_max": float(rows_rank.max() / step_s),
+                "rows_per_s_in_kernel_per_rank_mean": float((rows_rank / (rs[:, 2] / 1e3)).mean()),
+                "check": "pairs/s = rows_per_s_per_rank_max * n_gpus / (64 * (1 + 3 * retry_fraction))"
+                         " when the retry rows are dealt evenly"}
+
     line = {
         "metric": "registered pairs/sec (2048-pt, HOUV full)", "value": value, "unit": "pairs/s",
         "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
@@ -341,34 +517,62 @@ def run_ours(args):
                 "h2d_bytes_per_step": int(h_src.numel() * 4 * 2 + h_gt.numel() * 4),
                 "d2h_bytes_per_step": int(h_out.numel() * 4)},
         "gpu_launches": launches,
-        "roofline": {"bound": "fp32", "kernel": "houv::pose_sym_kernel (K3, symmetric scan)",
-                     "achieved": kflop / kms / 1e9, "peak": fp32_peak, "unit": "TFLOP/s",
-                     "frac": kflop / kms / 1e9 / fp32_peak, "traffic": traffic,
+        "workload": workload_stats(rstats, ms_dev, args.steps, P),
+        "roofline": {"bound": "fp32", "kernel": "houv::pose_duo_kernel (K3: symmetric scan, two rows "
+                                                "of a pair per CTA)",
+                     "achieved": kexec / kms / 1e9, "peak": fp32_peak, "unit": "TFLOP/s",
+                     "frac": kexec / kms / 1e9 / fp32_peak, "traffic": traffic,
+                     "traffic_source": traffic_src,
                      "peak_source": "FFMA-chain probe run in this process (MEASURED_PEAKS.json "
                                     "holds no FP32 CUDA-core figure)",
-                     "basis": "algorithmic: 13 FLOP x 2*N*M directed four-metric point pairs per "
-                              "row-iteration (SURVEY 8d); the kernel shares one evaluation between "
-                              "the two directions, so executed_tflops is half of achieved",
-                     "executed_tflops": kexec / kms / 1e9,
-                     "executed_frac": kexec / kms / 1e9 / fp32_peak,
+                     "basis": "EXECUTED: 13 FLOP per undirected four-metric point pair, N*M pairs per "
+                              "row-iteration -- the kernel evaluates d(i,j) once for both directions. "
+                              "SURVEY 8(d)'s directed-pair figure (26*N*M, what two scans would "
+                              "execute) is algorithmic_*; the reference's own arithmetic for the "
+                              "same result (8 searches x 8 FLOP) is ref_equiv_tflops",
+                     "algorithmic_tflops": kflop / kms / 1e9,
+                     "algorithmic_frac": kflop / kms / 1e9 / fp32_peak,
                      "ref_equiv_tflops": kref / kms / 1e9,
                      # 9 FMA-pipe + 8 ALU-pipe (min) lane-cycles per evaluation; the two pipes
-                     # share register-file operand bandwidth and add up (tools/ubench/pipes.cu)
+                     # share register-file operand bandwidth and largely add up (tools/ubench/pipes.cu):
+                     # this is the fraction of the SM's lane-cycles the kernel's math occupies
                      "math_pipe_cycles_frac": (17.0 * kunits / (kms * 1e-3 * clocks["sm_mhz"] * 1e6
                                                                 * 148 * 128))
                      if clocks and clocks.get("sm_mhz") else None,
                      "kernel_ms_per_launch": kms / max(len(ktim), 1),
                      "kernel_share_of_step": kms / ms_dev,
-                     "flop_per_launch": kflop / max(len(ktim), 1)},
+                     "flop_per_launch": kexec / max(len(ktim), 1)},
         "clocks": clocks,
         "quality": {"rot_err_deg_mean": float(met[:, 0].mean()),
                     "rot_err_deg_median": float(np.median(met[:, 0])),
                     "trans_err_mean": float(met[:, 1].mean()),
                     "mse_mean": float(met[:, 2].mean())},
     }
+    hard_pairs = P * world
+    line["extra"] = {"hard_set": dict(
+        workload="same step on synth.make_pairs(radius=1.0): objects of twice the size, same pose "
+                 "distribution; one untimed warm-up, one timed step",
+        pairs_per_s=hard_pairs / (ms_hard / 1e3), ms_per_step=ms_hard,
+        rot_err_deg_mean=float(met_hard[:, 0].mean()),
+        rot_err_deg_median=float(np.median(met_hard[:, 0])),
+        trans_err_mean=float(met_hard[:, 1].mean()), mse_mean=float(met_hard[:, 2].mean()),
+        **workload_stats(hstats, ms_hard, 1, P))}
+    if balance_identical is not None:
+        line["extra"]["balance_identical"] = balance_identical
+    if world > 1:
+        line["extra"]["note_vs_reference"] = ("the CPU arm runs on rank 0's host only and does not "
+                                              "scale with N: quote the N=1 ratio")
+    try:
+        line["parity_checked"] = parity_summary()
+    except Exception as e:  # the fixture travels with the repo; say so if it does not
+        line["parity_checked"] = {"error": repr(e)}
     # second half of BASELINE.json's metric: Chamfer NN throughput of the operator on its own
     # (K1; chamfer_3DDist forward, both directions), directed point pairs per second
-    line["chamfer_nn"] = chamfer_nn_lines(dev, flush, fp32_peak)
+    line["chamfer_nn"] = chamfer_operator_lines(dev, flush, fp32_peak)
+    try:
+        line["extra"]["icp_c3"] = icp_line(dev, flush)
+    except Exception as e:
+        line["extra"]["icp_c3"] = {"error": repr(e)}
     if world == 1 and not args.no_cpu_baseline:
         cores = os.cpu_count() or 1
         torch.set_num_threads(cores)
@@ -379,8 +583,9 @@ def run_ours(args):
             "value": cpu_pairs_per_s(sec, n_it), "unit": "pairs/s", "cores": cores,
             "kind": "port",
             "sample": "1 pair x %d starts x %d of %d Adam iterations at angle_base 0 in %.1f s "
-                      "(CPU oracle: restated houv.py over the C chamfer oracle on %d threads), "
-                      "linearly extrapolated, retries not added" % (KERNEL, n_it, ITERS, sec, cores)}
+                      "(CPU oracle: restated houv.py in torch-CPU over the C chamfer restatement, "
+                      "AVX2, %d threads), linearly extrapolated, retries not added"
+                      % (KERNEL, n_it, ITERS, sec, cores)}
     sys.stdout.flush()
     os.dup2(real_stdout, 1)
     print(json.dumps(line))

@@ -25,6 +25,10 @@ W_3D, W_VIEW, ALPHA = 6.0, 1.0, 0.5  # houv.py:209,222
 # When set to a list, every K3 launch appends (start_event, end_event, rows, iters, N)
 # recorded on the launching stream: bench.py derives the kernel's roofline from it.
 KERNEL_TIMING = None
+# What the last solve_model_batches call did on this rank: pairs, pairs sent through the retry
+# cascade (best min_1 above 0.030 after angle_base 0), rows of its first-pass and retry launches
+# (the retry rows this rank RAN, which differ from the ones it owns when rows are dealt over ranks).
+LAST_STATS = {}
 
 
 def initial_parameters(rows, seed=2021):
@@ -366,6 +370,9 @@ def solve_model_batches(src, src_rotated, batch_size=50, kernel=64, num_epochs=2
     rmse = rmse_loss.min(dim=1).values
     lst_add = torch.nonzero(rmse > RETRY_THRESHOLD).reshape(-1)  # ascending = batch order
     n_add = int(lst_add.numel())
+    LAST_STATS.clear()
+    LAST_STATS.update(pairs=P, retried_pairs=n_add, rows_first=P * kernel,
+                      rows_retry_owned=3 * n_add * kernel)
     if n_add > 0 or balance:
         batch_of = (lst_add // batch_size).cpu()
         counts = torch.bincount(batch_of, minlength=len(bounds)).tolist()

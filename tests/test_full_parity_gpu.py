@@ -38,7 +38,7 @@ def test_traces_follow_the_reference(report):
     for k in ("20", "50", "100", "200"):
         assert cp[k]["frac_within_1e_3"] >= env[k]["frac_within_1e_3"] - 0.10
         assert cp[k]["frac_within_1e_4"] >= env[k]["frac_within_1e_4"] - 0.15
-        assert cp[k]["median_rel"] <= max(3.0 * env[k]["median_rel"], 1e-6)
+        assert cp[k]["median_rel"] <= max(3.0 * env[k]["median_rel"], 2e-4)
     assert cp["200"]["median_rel"] <= 1e-3       # the typical start is still on the trajectory
 
 
