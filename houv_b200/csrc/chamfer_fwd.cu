@@ -234,7 +234,8 @@ extern "C" size_t houv_chamfer3d_workspace_bytes(int B, int N, int M) {
     const int nr = N >= M ? N : M, nc = N >= M ? M : N;
     // column keys when the rows span several CTAs, row keys when the columns are split
     const size_t n_c = nr > kSymChunkRows ? (size_t)B * (size_t)nc : 0;
-    const size_t n_r = sym_col_splits(B, nr, nc) > 1 ? (size_t)B * (size_t)nr : 0;
+    const int splits = sym_col_splits(B, nr, nc);  // one plane of row keys per column slice
+    const size_t n_r = splits > 1 ? (size_t)splits * (size_t)B * (size_t)nr : 0;
     return sizeof(unsigned long long) * (n_c + n_r);
 }
 

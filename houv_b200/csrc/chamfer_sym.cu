@@ -122,8 +122,13 @@ __global__ void __launch_bounds__(kSThreads, 2) chamfer_sym_kernel(const SymArgs
     const int nr = A.nr, nc = A.nc;
     const int c_lo = blockIdx.z * A.cols_per_split;          // this CTA's slice of the columns
     const int c_hi = min(nc, c_lo + A.cols_per_split);
-    if (c_lo >= nc) return;
     const int nrows = min(kSRows, nr - rbase);  // real rows of this chunk (> 0 by grid size)
+    if (c_lo >= nc) {  // a slice past the last column (slices are rounded up to 64): its plane of row keys is +inf
+        for (int b = blockIdx.y; b < A.B; b += gridDim.y)
+            for (int i = t; i < nrows; i += kSThreads)
+                A.row_keys[((size_t)blockIdx.z * A.B + b) * nr + rbase + i] = ~0ull;
+        return;
+    }
     const bool scan_active = 256 * w < nrows;   // warp-uniform
     const int nsg = (nrows + kSGrp - 1) / kSGrp;
     const float inf = __int_as_float(0x7f800000);
@@ -299,9 +304,12 @@ __global__ void __launch_bounds__(kSThreads, 2) chamfer_sym_kernel(const SymArgs
             const int i = row0 + r;
             if (i < nrows) {
                 const size_t o = (size_t)b * nr + rbase + i;
-                if (A.row_keys) {  // smallest distance, then earliest superblock: it holds the first minimum
-                    atomicMin(A.row_keys + o, ((unsigned long long)__float_as_uint(best[r]) << 32) |
-                                                  (unsigned)gid[r]);
+                if (A.row_keys) {
+                    // column slices: every slice has its own plane of (distance, superblock) keys --
+                    // plain stores, nothing to initialise; the unpack takes the smallest key over the
+                    // planes (smallest distance, then earliest superblock: it holds the first minimum)
+                    A.row_keys[(size_t)blockIdx.z * A.B * nr + o] =
+                        ((unsigned long long)__float_as_uint(best[r]) << 32) | (unsigned)gid[r];
                 } else {
                     A.dist_r[o] = best[r];
                     A.idx_r[o] = idxr[r];
@@ -313,13 +321,12 @@ __global__ void __launch_bounds__(kSThreads, 2) chamfer_sym_kernel(const SymArgs
 
 // Column keys hold (distance, row index); row keys hold (distance, superblock of 64 columns): the row's
 // first minimum is the first column of that superblock whose distance equals the minimum.  Blocks
-// [0, col_blocks) unpack 256 column keys each, the others recover 8 rows each, one warp per row (the 64
-// candidates are 768 contiguous bytes; lane l looks at candidates 2l and 2l+1).
+// [0, col_blocks) unpack 256 column keys each, the others recover 32 rows each, eight lanes per row.
 __global__ void __launch_bounds__(256) chamfer_sym_unpack(const unsigned long long *keys, float *dist, int *idx,
                                                          size_t n, unsigned col_blocks,
-                                                         const unsigned long long *row_keys, float *dist_r,
-                                                         int *idx_r, size_t n_r, const float *rows,
-                                                         const float *cols, int nr, int nc) {
+                                                         const unsigned long long *row_keys, int planes,
+                                                         float *dist_r, int *idx_r, size_t n_r,
+                                                         const float *rows, const float *cols, int nr, int nc) {
     if (blockIdx.x < col_blocks) {
         const size_t i = (size_t)blockIdx.x * 256 + threadIdx.x;
         if (i < n) {
@@ -329,27 +336,54 @@ __global__ void __launch_bounds__(256) chamfer_sym_unpack(const unsigned long lo
         }
         return;
     }
-    const size_t i = (size_t)(blockIdx.x - col_blocks) * 8 + (threadIdx.x >> 5);
-    if (i >= n_r) return;
-    const int lane = threadIdx.x & 31;
-    const unsigned long long k = row_keys[i];
+    // eight lanes per row: lane `sub` reads the planes sub, sub+8, .. of the row's key and then the
+    // candidates 8 sub .. 8 sub + 7 of the winning superblock (96 contiguous bytes, LDG.128 when the
+    // cloud is 16-byte aligned) -- two dependent round trips per row, every load of a stage in flight
+    // at once; the lowest matching candidate over the eight lanes is the first minimum
+    const size_t i = (size_t)(blockIdx.x - col_blocks) * 32 + (threadIdx.x >> 3);
+    const int sub = threadIdx.x & 7;
+    const bool active = i < n_r;
+    unsigned long long k = ~0ull;
+    if (active)
+        for (int z = sub; z < planes; z += 8) {
+            const unsigned long long kz = row_keys[(size_t)z * n_r + i];
+            k = kz < k ? kz : k;
+        }
+#pragma unroll
+    for (int o = 1; o < 8; o <<= 1) {
+        const unsigned long long ko = __shfl_xor_sync(0xffffffffu, k, o);
+        k = ko < k ? ko : k;
+    }
     const float target = __uint_as_float((unsigned)(k >> 32));
     const int j0 = (int)(unsigned)(k & 0xffffffffull) * kSGrp;
-    const size_t b = i / nr;
-    const float qx = __ldg(rows + 3 * i), qy = __ldg(rows + 3 * i + 1), qz = __ldg(rows + 3 * i + 2);
-    const float *c = cols + (b * nc + j0) * 3;
-    const int m = min(kSGrp, nc - j0);
-    bool hit0 = false, hit1 = false;
-    if (2 * lane < m)
-        hit0 = sqdist_ref(__ldg(c + 6 * lane), __ldg(c + 6 * lane + 1), __ldg(c + 6 * lane + 2), qx, qy, qz) == target;
-    if (2 * lane + 1 < m)
-        hit1 = sqdist_ref(__ldg(c + 6 * lane + 3), __ldg(c + 6 * lane + 4), __ldg(c + 6 * lane + 5), qx, qy, qz) == target;
-    const unsigned any = __ballot_sync(0xffffffffu, hit0 || hit1);
-    if (lane == 0) {
-        dist_r[i] = target;
-        idx_r[i] = j0;  // a row that never improved (no finite distance) keeps the superblock's first index
+    int first = kSGrp;
+    if (active) {
+        const size_t b = i / nr;
+        const float qx = __ldg(rows + 3 * i), qy = __ldg(rows + 3 * i + 1), qz = __ldg(rows + 3 * i + 2);
+        const float *c = cols + (b * nc + j0 + 8 * sub) * 3;
+        const int m = min(8, nc - j0 - 8 * sub);
+        if (m == 8 && (reinterpret_cast<uintptr_t>(c) & 15) == 0) {
+            float4 v[6];
+#pragma unroll
+            for (int q = 0; q < 6; ++q) v[q] = __ldg(reinterpret_cast<const float4 *>(c) + q);
+            const float *f = reinterpret_cast<const float *>(v);
+#pragma unroll
+            for (int pnt = 7; pnt >= 0; --pnt)
+                if (sqdist_ref(f[3 * pnt], f[3 * pnt + 1], f[3 * pnt + 2], qx, qy, qz) == target)
+                    first = 8 * sub + pnt;
+        } else {
+            for (int pnt = m - 1; pnt >= 0; --pnt)
+                if (sqdist_ref(__ldg(c + 3 * pnt), __ldg(c + 3 * pnt + 1), __ldg(c + 3 * pnt + 2), qx, qy, qz) == target)
+                    first = 8 * sub + pnt;
+        }
     }
-    if (any && lane == __ffs(any) - 1) idx_r[i] = j0 + 2 * lane + (hit0 ? 0 : 1);
+#pragma unroll
+    for (int o = 1; o < 8; o <<= 1) first = min(first, __shfl_xor_sync(0xffffffffu, first, o));
+    if (active && sub == 0) {
+        dist_r[i] = target;
+        // a row that never improved (no finite distance) keeps the superblock's first index
+        idx_r[i] = first >= kSGrp ? j0 : j0 + first;
+    }
 }
 
 int sym_col_splits(int B, int nr, int nc) {
@@ -358,14 +392,14 @@ int sym_col_splits(int B, int nr, int nc) {
     // two CTAs per SM (measured, C2 = 32 x 2048^2: 8 slices 66.6 us, 4 slices 68.6 us, directed kernel
     // 74.7 us; batches that already fill the GPU lose from slicing, C5: 0.71 ms with 4 slices, 0.665 without)
     int s = forced > 0 ? forced : (ctas >= 148 ? 1 : (int)(296 / ctas));
-    const int most = nc / 256;  // at least 256 columns per slice
+    const int most = forced > 0 ? nc / 64 : nc / 256;  // at least 256 columns per slice
     if (s > most) s = most;
     return s < 1 ? 1 : s;
 }
 
 // Launch the symmetric forward with `rows` = the cloud chunked over CTAs.  a.keys: workspace of
-// B*nc 64-bit words, required when nr > kSRows; a.row_keys: B*nr words, required when
-// sym_col_splits() > 1.
+// B*nc 64-bit words, required when nr > kSRows; a.row_keys: sym_col_splits() planes of B*nr words,
+// required when sym_col_splits() > 1.
 int launch_chamfer_sym(const SymArgs &a, cudaStream_t st) {
     static unsigned long long smem_set = 0;  // per-device flag bits
     if (int e = ensure_dyn_smem(chamfer_sym_kernel<8>, (int)sizeof(SmemK1s), smem_set)) return e;
@@ -379,16 +413,15 @@ int launch_chamfer_sym(const SymArgs &a, cudaStream_t st) {
     const size_t n_c = chunks > 1 ? (size_t)a.B * a.nc : 0, n_r = splits > 1 ? (size_t)a.B * a.nr : 0;
     cudaError_t e = cudaSuccess;
     if (n_c) e = cudaMemsetAsync(k.keys, 0xff, sizeof(unsigned long long) * n_c, st);
-    if (e == cudaSuccess && n_r) e = cudaMemsetAsync(k.row_keys, 0xff, sizeof(unsigned long long) * n_r, st);
-    if (e != cudaSuccess) return (int)e;
+    if (e != cudaSuccess) return (int)e;  // (the row-key planes are written whole: no initialisation)
     dim3 grid(chunks, a.B < 65535 ? a.B : 65535, splits);
     chamfer_sym_kernel<8><<<grid, kSThreads, sizeof(SmemK1s), st>>>(k);
     if (int err = check_launch()) return err;
     if (n_c + n_r) {
-        const unsigned col_blocks = (unsigned)((n_c + 255) / 256), row_blocks = (unsigned)((n_r + 7) / 8);
+        const unsigned col_blocks = (unsigned)((n_c + 255) / 256), row_blocks = (unsigned)((n_r + 31) / 32);
         chamfer_sym_unpack<<<col_blocks + row_blocks, 256, 0, st>>>(k.keys, a.dist_c, a.idx_c, n_c, col_blocks,
-                                                                   k.row_keys, a.dist_r, a.idx_r, n_r, a.rows,
-                                                                   a.cols, a.nr, a.nc);
+                                                                   k.row_keys, splits, a.dist_r, a.idx_r, n_r,
+                                                                   a.rows, a.cols, a.nr, a.nc);
         return check_launch();
     }
     return 0;

@@ -37,6 +37,8 @@ struct PoseArgs {
     const float *row_scale;  // [rows] per-row grad_scale, or null (= grad_scale)
     // one-row kernels only: skip every row that pose_duo_kernel took (rows 2b, 2b+1 of one pair)
     int only_unpaired;
+    int row_begin;  // one-row kernels only: CTA b works on row row_begin + b
+    int grid_rows;  // one-row kernels only: CTAs to launch (0 = rows)
 };
 
 __device__ __forceinline__ bool row_is_paired(const PoseArgs &A, int row) {
@@ -226,6 +228,6 @@ __device__ __forceinline__ void state_store(const PoseState &st, const PoseArgs 
 }
 
 int launch_pose_sym(const PoseArgs &a, int unroll, cudaStream_t st);  // pose_sym.cu
-int launch_pose_duo(const PoseArgs &a, cudaStream_t st);              // pose_duo.cu
+int launch_pose_duo(const PoseArgs &a, bool pipelined, cudaStream_t st);  // pose_duo.cu
 
 }  // namespace houv

@@ -37,12 +37,17 @@ namespace houv {
 
 constexpr int kDuoThreads = 512;
 constexpr int kTeam = 256;  // threads per team = per row
+// pipelined column reduction (kPipe): four buffers of partial column minima, one per 16-column
+// phase: [metric][sub-group][16 columns], metric stride padded so that the reducer's lanes (two
+// metrics x 16 columns) fall into 32 different banks
+constexpr int kPartM = 32 * 16 + 16;   // floats per metric
+constexpr int kPartBuf = 4 * kPartM;   // floats per buffer
 
 struct TeamSmem {
     // inside the sweep: part[sub-group][metric][column], partial column minima of one superblock;
     // outside: yx, yy, yz (transformed source, consecutive kPts-float arrays: the recovery addresses
     // y and z as x + kPts, x + 2*kPts) and d3r (3-D row minima, dist2)
-    float region[4 * kPts];
+    float region[4 * kPartBuf > 4 * kPts ? 4 * kPartBuf : 4 * kPts];
     float d3c[kPts];                  // 3-D column minima (dist1)
     unsigned char gid[4][2][kPts];    // winning group: [m][0][col] = 64-row sub-group, [m][1][row] = superblock
     // row minima as of the last superblock boundary: per thread 8 float4 chunks, chunk c = values
@@ -54,12 +59,39 @@ struct TeamSmem {
     unsigned selu[8];
     double state[80];                 // PoseState of this row (touched by the team's thread 0 only)
     double bt[2];
+    // kPipe: full[b] -- all 8 warps stored their partial minima of the phase in buffer b;
+    // empty[b] -- its two reducer warps are done with it
+    unsigned long long full[4], empty[4];
+    float vbuf[2][4][kSB];            // kPipe: view column sums [upper half][metric][column] on their way to team_sum
 };
 
 struct DuoSmem {
     float tx[kPts], ty[kPts], tz[kPts];  // target cloud (columns) of the pair, shared by both teams
     TeamSmem team[2];
 };
+
+__device__ __forceinline__ unsigned duo_smem_u32(const void *p) {
+    return (unsigned)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ void duo_mbar_init(unsigned long long *bar, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(duo_smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void duo_mbar_arrive(unsigned long long *bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(duo_smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void duo_mbar_wait(unsigned long long *bar, unsigned parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONE_%=;\n"
+        "bra WAIT_%=;\n"
+        "DONE_%=:\n"
+        "}\n" ::"r"(duo_smem_u32(bar)),
+        "r"(parity)
+        : "memory");
+}
 
 __device__ __forceinline__ void team_sync(int team) {
     asm volatile("bar.sync %0, %1;" ::"r"(team + 1), "r"(kTeam) : "memory");
@@ -102,7 +134,7 @@ __device__ __forceinline__ void team_sum(float (&a)[NV], float (&b)[NV], unsigne
     }
 }
 
-template <int kSymUnroll, int kRG>
+template <int kSymUnroll, int kRG, bool kPipe>
 __global__ void __launch_bounds__(kDuoThreads, 1) pose_duo_kernel(const PoseArgs A) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     DuoSmem &S = *reinterpret_cast<DuoSmem *>(smem_raw);
@@ -161,7 +193,15 @@ __global__ void __launch_bounds__(kDuoThreads, 1) pose_duo_kernel(const PoseArgs
             state_load(st, A, row);
             b1t = pow(A.beta1, (double)A.step0);
             b2t = pow(A.beta2, (double)A.step0);
+            if (kPipe) {
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    duo_mbar_init(&T.full[i], kTeam / 32);  // one arrival per warp
+                    duo_mbar_init(&T.empty[i], 2);          // the two reducer warps of the phase
+                }
+            }
         }
+        int gs = 0;  // kPipe: phases swept by this team so far (all iterations), buffer = gs & 3
         __syncthreads();
         // team 1 starts half a sweep late (released from inside team 0's first sweep), so that from
         // then on one team's phases outside the sweep fall into the other team's sweep
@@ -216,6 +256,7 @@ __global__ void __launch_bounds__(kDuoThreads, 1) pose_duo_kernel(const PoseArgs
             float vcolA = 0.f, vcolB = 0.f;  // sum sqrt(column minimum) of view metric rm, lower / upper superblocks
             team_sync(team);
 
+            if constexpr (!kPipe) {
 #pragma unroll 1
             for (int sb = 0; sb < nsb; ++sb) {
                 if (scan_active) {
@@ -288,6 +329,133 @@ __global__ void __launch_bounds__(kDuoThreads, 1) pose_duo_kernel(const PoseArgs
                     }
                 }
                 team_sync(team);
+            }
+            } else {
+                // ---- pipelined form: every 16-column phase has its own buffer of partial column
+                // minima (4 buffers); the warps never stop at a barrier inside the sweep.  After
+                // its phase gs a warp arrives on full[gs & 3]; the two warps whose turn it is
+                // (warps 2*ph, 2*ph+1 for the phase ph = (gs-1) & 3 just behind) wait for that
+                // buffer to be complete, reduce its 4 metrics x 16 columns over the 32 sub-groups
+                // and release it (empty), which every warp checks before storing phase gs + 3.
+                // All groups of a warp take the SAME 16-column block in a phase (ascending), so a
+                // buffer is complete after one phase.
+                const int gs0 = gs;  // a multiple of 4: (gs & 3) is the phase inside the superblock
+                auto reduce_phase = [&](int p) {
+                    const int b = p & 3, pl = p - gs0, sbp = pl >> 2, php = pl & 3;
+                    duo_mbar_wait(&T.full[b], (unsigned)(p >> 2) & 1u);
+                    const int m = (u >> 4) & 3, c16 = u & 15;
+                    const float *pp = T.region + b * kPartBuf + m * kPartM + c16;
+                    float bv = kInf;
+                    int bs = 0;
+                    if (nsg == 32) {
+                        // minimum of each chunk of 8 sub-groups (FMNMX3 tree), first chunk holding
+                        // the overall minimum (ascending, strict '<'), then its first sub-group
+                        int bc = 0;
+#pragma unroll
+                        for (int c = 0; c < 4; ++c) {
+                            float v[8];
+#pragma unroll
+                            for (int k = 0; k < 8; ++k) v[k] = pp[(8 * c + k) * 16];
+                            const float cm = min3(min3(v[0], v[1], v[2]), min3(v[3], v[4], v[5]),
+                                                  fminf(v[6], v[7]));
+                            if (cm < bv) { bv = cm; bc = c; }
+                        }
+                        const float *pc8 = pp + bc * 128;
+                        bs = 8 * bc;
+#pragma unroll
+                        for (int k = 7; k >= 0; --k)
+                            if (pc8[k * 16] == bv) bs = 8 * bc + k;
+                    } else {
+                        for (int g = 0; g < nsg; ++g) {
+                            const float v = pp[g * 16];
+                            if (v < bv) { bv = v; bs = g; }
+                        }
+                    }
+                    const int col = sbp * kSB + 16 * php + c16;
+                    T.gid[m][0][col] = (unsigned char)bs;
+                    if (m == 0) T.d3c[col] = bv;
+                    else if (col < M) {
+                        if (sbp < nsbh) vcolA += sqrtf(bv);
+                        else vcolB += sqrtf(bv);
+                    }
+                    __syncwarp();
+                    if (lane == 0) duo_mbar_arrive(&T.empty[b]);
+                };
+#pragma unroll 1
+                for (int sb = 0; sb < nsb; ++sb) {
+                    const int sbbase = sb * kSB;
+#pragma unroll 1
+                    for (int ph = 0; ph < 4; ++ph) {
+                        const int b = gs & 3;
+                        if (scan_active) {
+                            float cmx[4], cmy[4];  // running column minima of the pair in hand
+#pragma unroll
+                            for (int m = 0; m < 4; ++m) { cmx[m] = kInf; cmy[m] = kInf; }
+                            const int cbase = sbbase + 16 * ph;
+#pragma unroll kSymUnroll
+                            for (int s = 0; s < 8; ++s) {
+                                const int c = cbase + 2 * ((ll + s) & 7);
+                                const float2 X = *reinterpret_cast<const float2 *>(&S.tx[c]);
+                                const float2 Y = *reinterpret_cast<const float2 *>(&S.ty[c]);
+                                const float2 Z = *reinterpret_cast<const float2 *>(&S.tz[c]);
+                                sym_step<kRG, 4>(X, Y, Z, nqx, nqy, nqz, best, cmx, cmy);
+                                if (s < 7) {
+#pragma unroll
+                                    for (int m = 0; m < 4; ++m) {
+                                        cmx[m] = __shfl_sync(0xffffffffu, cmx[m], ll + 1, 8);
+                                        cmy[m] = __shfl_sync(0xffffffffu, cmy[m], ll + 1, 8);
+                                    }
+                                }
+                            }
+                            // buffer b was last used by phase gs - 4: reduced by now?
+                            if (gs >= 4) duo_mbar_wait(&T.empty[b], (unsigned)((gs >> 2) - 1) & 1u);
+                            float *pw = T.region + b * kPartBuf + sg * 16 + 2 * ((ll + 7) & 7);
+#pragma unroll
+                            for (int m = 0; m < 4; ++m)
+                                *reinterpret_cast<float2 *>(pw + m * kPartM) = make_float2(cmx[m], cmy[m]);
+                        } else if (gs >= 4) {
+                            // warps without rows store nothing but keep in step: an early arrival
+                            // would be counted towards the buffer's previous use
+                            duo_mbar_wait(&T.empty[b], (unsigned)((gs >> 2) - 1) & 1u);
+                        }
+                        __syncwarp();
+                        if (lane == 0) duo_mbar_arrive(&T.full[b]);
+                        if (gs > gs0 && ((gs - 1) & 3) == (u >> 6)) reduce_phase(gs - 1);
+                        ++gs;
+                    }
+                    if (scan_active) {
+                        unsigned improved = 0;
+#pragma unroll
+                        for (int c = 0; c < 8; ++c) {
+                            const int m = c >> 1, r0 = 4 * (c & 1);
+                            float4 &slot = T.shadow[u][c ^ (u & 7)];
+                            const float4 pv = slot;
+                            improved |= (best[m][r0 + 0] < pv.x ? 1u : 0u) << (4 * c + 0);
+                            improved |= (best[m][r0 + 1] < pv.y ? 1u : 0u) << (4 * c + 1);
+                            improved |= (best[m][r0 + 2] < pv.z ? 1u : 0u) << (4 * c + 2);
+                            improved |= (best[m][r0 + 3] < pv.w ? 1u : 0u) << (4 * c + 3);
+                            slot = make_float4(best[m][r0], best[m][r0 + 1], best[m][r0 + 2], best[m][r0 + 3]);
+                        }
+                        while (improved) {
+                            const int k = __ffs(improved) - 1;
+                            improved &= improved - 1;
+                            T.gid[k >> 3][1][row0 + (k & 7)] = (unsigned char)sb;
+                        }
+                    }
+                    if (team == 0 && it == 0 && sb == (nsb >> 1))
+                        asm volatile("bar.arrive 3, %0;" ::"r"(kDuoThreads) : "memory");
+                }
+                if (((gs - 1) & 3) == (u >> 6)) reduce_phase(gs - 1);  // the last phase
+                // the view column sums go to the threads team_sum expects them in (metric u >> 6,
+                // column u & 63); this thread reduced metric (u >> 4) & 3, column 16 (u >> 6) + (u & 15)
+                {
+                    const int m = (u >> 4) & 3, col = 16 * (u >> 6) + (u & 15);
+                    T.vbuf[0][m][col] = vcolA;
+                    T.vbuf[1][m][col] = vcolB;
+                }
+                team_sync(team);
+                vcolA = T.vbuf[0][rm][rc];
+                vcolB = T.vbuf[1][rm][rc];
             }
 
             // ---- (d) the region becomes the transformed source again (+ the 3-D row minima)
@@ -543,24 +711,54 @@ __global__ void __launch_bounds__(kDuoThreads, 1) pose_duo_kernel(const PoseArgs
     }
 }
 
-template <int kU, int kRG>
+static int sm_count() {
+    static int cached[64] = {0};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev >= 64) return 148;
+    if (!cached[dev]) {
+        int n = 0;
+        cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+        cached[dev] = n > 0 ? n : 148;
+    }
+    return cached[dev];
+}
+
+template <int kU, int kRG, bool kPipe>
 static int launch_duo(const PoseArgs &a, cudaStream_t st) {
     static unsigned long long smem_set = 0;  // per-device flag bits
-    if (int e = ensure_dyn_smem(pose_duo_kernel<kU, kRG>, (int)sizeof(DuoSmem), smem_set)) return e;
-    if (a.rows >= 2) {
-        pose_duo_kernel<kU, kRG><<<a.rows / 2, kDuoThreads, sizeof(DuoSmem), st>>>(a);
+    if (int e = ensure_dyn_smem(pose_duo_kernel<kU, kRG, kPipe>, (int)sizeof(DuoSmem), smem_set)) return e;
+    // One CTA per SM, two rows per CTA: whole waves of two-row CTAs, then -- when what is left fits
+    // one wave of ONE-row CTAs (which lasts ~0.55 of a two-row wave) -- the rest, and an odd last
+    // row, through pose_sym_kernel.  Same bits either way.
+    const int sms = sm_count();
+    int nduo = a.rows / 2;
+    const int whole = nduo / sms * sms;
+    if (whole > 0 && a.rows - 2 * whole <= sms) nduo = whole;
+    if (nduo > 0) {
+        pose_duo_kernel<kU, kRG, kPipe><<<nduo, kDuoThreads, sizeof(DuoSmem), st>>>(a);
         if (int e = check_launch()) return e;
+        // rows without a partner of the same pair (neighbours of different pairs in a caller-made
+        // row_pair, odd K): the one-row kernel on exactly those, every other CTA exits at once
+        if (a.row_pair || (a.K & 1)) {
+            PoseArgs b = a;
+            b.only_unpaired = 1;
+            b.grid_rows = 2 * nduo;
+            if (int e = launch_pose_sym(b, 84, st)) return e;
+        }
     }
-    // rows without a partner of the same pair (an odd tail; neighbours of different pairs in a
-    // caller-made row_pair): the one-row kernel with the same bits, every other CTA exits at once
-    if (a.row_pair || (a.K & 1) || (a.rows & 1)) {
+    if (a.rows > 2 * nduo) {
         PoseArgs b = a;
-        b.only_unpaired = 1;
+        b.row_begin = 2 * nduo;
+        b.grid_rows = a.rows - 2 * nduo;
         return launch_pose_sym(b, 84, st);
     }
     return 0;
 }
 
-int launch_pose_duo(const PoseArgs &a, cudaStream_t st) { return launch_duo<8, 4>(a, st); }
+// pipelined = column reduction overlapped with the sweep (variant 21); else one barrier pair per
+// superblock (variant 20)
+int launch_pose_duo(const PoseArgs &a, bool pipelined, cudaStream_t st) {
+    return pipelined ? launch_duo<8, 4, true>(a, st) : launch_duo<8, 4, false>(a, st);
+}
 
 }  // namespace houv

@@ -455,6 +455,8 @@ extern "C" int houv_pose_optimise_ex(const HouvPoseProblem *q, void *stream) {
     a.tran_s_out = q->tran_s_out; a.trace = q->trace; a.row_pair = q->row_pair; a.row_base = q->row_base;
     a.row_scale = q->row_scale;
     a.only_unpaired = 0;
+    a.row_begin = 0;
+    a.grid_rows = 0;
     a.P = q->P; a.N = q->N; a.M = q->M; a.K = q->K; a.rows = rows;
     a.step0 = q->step0; a.iters = q->iters; a.angle_base = q->angle_base;
     a.k3d = (int)((double)q->N * (double)q->percent);
@@ -470,7 +472,9 @@ extern "C" int houv_pose_optimise_ex(const HouvPoseProblem *q, void *stream) {
     switch (g_pose_variant) {
         case 20:  // two rows of a pair per CTA (pose_duo.cu); a loss without view terms keeps the
                   // one-metric kernel, which already runs two CTAs per SM
-            return a.wview == 0.f ? launch_pose_sym(a, 84, st) : launch_pose_duo(a, st);
+            return a.wview == 0.f ? launch_pose_sym(a, 84, st) : launch_pose_duo(a, false, st);
+        case 21:  // the same with the column reduction pipelined under the sweep
+            return a.wview == 0.f ? launch_pose_sym(a, 84, st) : launch_pose_duo(a, true, st);
         case 10: return launch_pose_sym(a, 2, st);
         case 11: return launch_pose_sym(a, 4, st);
         case 12: return launch_pose_sym(a, 8, st);

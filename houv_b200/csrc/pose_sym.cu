@@ -101,7 +101,7 @@ __global__ void __launch_bounds__(kSymThreads, kNM == 1 ? 2 : 1) pose_sym_kernel
     constexpr int kSwz = SmemSym::kSlots - 1;  // shadow chunk swizzle mask
     SmemSym &S = *reinterpret_cast<SmemSym *>(smem_raw);
     const int t = threadIdx.x;
-    const int row = blockIdx.x;
+    const int row = A.row_begin + blockIdx.x;
     if (A.only_unpaired && row_is_paired(A, row)) return;
     const int pair = A.row_pair ? A.row_pair[row] : row / A.K;
     const int N = A.N, M = A.M;  // rows = source points, columns = target points
@@ -541,7 +541,9 @@ static int launch_sym(const PoseArgs &a, cudaStream_t st) {
     static unsigned long long smem_set = 0;  // per-device flag bits
     if (int e = ensure_dyn_smem(pose_sym_kernel<kU, kRG, kNM, kRecov>, (int)sizeof(SmemSymT<kNM>), smem_set))
         return e;
-    pose_sym_kernel<kU, kRG, kNM, kRecov><<<a.rows, kSymThreads, sizeof(SmemSymT<kNM>), st>>>(a);
+    // (the two-row launcher hands the rows it did not take to this kernel: grid_rows of them)
+    pose_sym_kernel<kU, kRG, kNM, kRecov><<<a.grid_rows > 0 ? a.grid_rows : a.rows, kSymThreads,
+                                            sizeof(SmemSymT<kNM>), st>>>(a);
     return check_launch();
 }
 

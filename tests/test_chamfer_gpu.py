@@ -59,7 +59,9 @@ def test_edge_cases(case):
 
 
 @pytest.mark.parametrize("shape", [(1, 1, 1), (2, 3, 9), (4, 100, 200), (2, 2048, 2048),
-                                   (1, 2049, 4100), (3, 777, 15), (70000, 2, 3)])
+                                   (1, 2049, 4100), (3, 777, 15), (70000, 2, 3),
+                                   # column slices: rounded up to 64, so the last ones are empty
+                                   (1, 4100, 4100), (5, 2048, 1100), (32, 2048, 2048)])
 def test_random_shapes_vs_oracle(shape):
     b, n, m = shape
     rng = np.random.RandomState(b * 31 + n)

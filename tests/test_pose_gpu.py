@@ -23,11 +23,13 @@ N_SMALL = 256
 KERNEL = 32
 
 
-@pytest.fixture(autouse=True, params=[20, 13, 0], ids=["k3-duo", "k3-symmetric", "k3-two-scans"])
+@pytest.fixture(autouse=True, params=[21, 20, 13, 0],
+                ids=["k3-duo-pipelined", "k3-duo", "k3-symmetric", "k3-two-scans"])
 def pose_variant(request):
-    """Every test of this module runs against all K3 kernels: two rows of a pair per CTA
-    (csrc/pose_duo.cu, the default), the symmetric scan with one row per CTA (csrc/pose_sym.cu)
-    and the two-directed-scans kernel (csrc/pose_opt.cu)."""
+    """Every test of this module runs against all K3 kernels: two rows of a pair per CTA with the
+    column reduction pipelined under the sweep (csrc/pose_duo.cu, kPipe) or at a barrier per
+    superblock, the symmetric scan with one row per CTA (csrc/pose_sym.cu) and the
+    two-directed-scans kernel (csrc/pose_opt.cu)."""
     from houv_b200 import _lib
     lib = _lib.load()
     lib.houv_set_pose_variant(request.param)
@@ -221,21 +223,23 @@ def test_equality_argmin_recovery_equals_distance_index_search(pose_variant, n, 
 
 
 @pytest.mark.parametrize("n,iters,pairs", [(2048, 4, 3), (256, 7, 2), (333, 5, 2), (1000, 3, 1),
-                                           (64, 4, 1), (1100, 3, 2)])
+                                           (64, 4, 1), (1100, 3, 2), (256, 3, 10)])
 def test_duo_equals_single_row_kernel(pose_variant, n, iters, pairs):
     """pose_duo_kernel (two rows of a pair per CTA, 256 threads per row, one team sweeping all
     superblocks) takes every floating-point sum in pose_sym_kernel's order: trace, outputs,
     parameters and both Adam moments identical bit for bit -- also with exact ties, with a cloud
-    size that is no multiple of 64 / 256, and resumed from a state."""
+    size that is no multiple of 64 / 256, resumed from a state, and with more two-row CTAs than SMs
+    (10 pairs x 32 starts = 160 CTAs: one whole wave of 148, the other 24 rows through the one-row
+    kernel in the same call)."""
     if pose_variant != 20:
-        pytest.skip("compares the two-row kernel with the one-row kernel")
+        pytest.skip("compares the two-row kernels with the one-row kernel")
     from houv_b200 import _lib, solver
     lib = _lib.load()
     src, tgt, _ = _pairs(21, pairs, n=n)
     src[:, 5] = src[:, 4]
     tgt[:, n - 1] = tgt[:, 3]
     res = []
-    for variant in (13, 20):
+    for variant in (13, 20, 21):
         lib.houv_set_pose_variant(variant)
         out, params, m, v = _gpu_run(src, tgt, iters)
         more = solver.pose_optimise(src.cuda(), tgt.cuda(), params, KERNEL, 2, adam_m=m, adam_v=v,
@@ -244,8 +248,9 @@ def test_duo_equals_single_row_kernel(pose_variant, n, iters, pairs):
                     out["loss"].clone(), more["trace"].clone(), more["T"].clone(), params.clone(),
                     m.clone(), v.clone()))
     lib.houv_set_pose_variant(20)
-    for a, b in zip(*res):
-        assert torch.equal(a, b)
+    for other in res[1:]:
+        for a, b in zip(res[0], other):
+            assert torch.equal(a, b)
 
 
 def test_duo_row_layouts(pose_variant):
@@ -264,7 +269,7 @@ def test_duo_row_layouts(pose_variant):
     row_scale = (torch.rand(rows, generator=g) + 0.5) / rows
     init = torch.from_numpy(solver.initial_parameters(64))[:rows].contiguous()
     res = []
-    for variant in (13, 20):
+    for variant in (13, 20, 21):
         lib.houv_set_pose_variant(variant)
         params = init.clone().cuda()
         out = solver.pose_optimise(src.cuda(), tgt.cuda(), params, KERNEL, 5, row_pair=row_pair.cuda(),
@@ -273,5 +278,6 @@ def test_duo_row_layouts(pose_variant):
         res.append((out["trace"].clone(), out["min_1"].clone(), out["R"].clone(), out["T"].clone(),
                     params.clone()))
     lib.houv_set_pose_variant(20)
-    for a, b in zip(*res):
-        assert torch.equal(a, b)
+    for other in res[1:]:
+        for a, b in zip(res[0], other):
+            assert torch.equal(a, b)
