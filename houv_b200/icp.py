@@ -33,6 +33,61 @@ class RegistrationResult:
         self.correspondences = correspondences
 
 
+RESIDENT_MAX_POINTS = 2048  # csrc/icp.cu kIcpPts: one CTA keeps a pair resident for all iterations
+
+
+def _registration_icp_large(source, target, max_distance, init, max_iteration, relative_fitness,
+                            relative_rmse):
+    """The same loop for clouds above RESIDENT_MAX_POINTS, which the resident kernel cannot hold:
+    per iteration one directed search of K1 (any size) over the pairs still iterating, the gated
+    sums and the Kabsch update in float64 on the device (batched SVD), convergence per pair.
+    Open3D takes any cloud size (train_ICP.py:148-151), so does this call."""
+    from .chamfer import nn_search
+    P, N, _ = source.shape
+    dev = source.device
+    T = (init.double() if init.dim() == 3 else init.double().expand(P, 4, 4)).clone()
+    thr2 = float(max_distance) ** 2
+    srcd = source.double()
+
+    def evaluate(idx, Tm):
+        y = torch.bmm(srcd[idx], Tm[:, :3, :3].transpose(1, 2)) + Tm[:, :3, 3].unsqueeze(1)
+        d, j = nn_search(y.float().contiguous(), target[idx].contiguous())
+        keep = (d < thr2)
+        n = keep.sum(1)
+        fit = n.double() / N
+        rm = torch.sqrt((d.double() * keep).sum(1) / n.clamp(min=1).double()) * (n > 0)
+        w = torch.gather(target[idx].double(), 1, j.long().unsqueeze(2).expand(-1, -1, 3))
+        return fit, rm, n, y, w, keep.double()
+
+    every = torch.arange(P, device=dev)
+    fit, rm, ncorr, y, w, keep = evaluate(every, T)
+    its = torch.zeros(P, device=dev)
+    idx = every
+    for i in range(max_iteration):
+        if idx.numel() == 0:
+            break
+        n = keep.sum(1, keepdim=True).clamp(min=1.0)
+        ym, wm = (y * keep.unsqueeze(2)).sum(1) / n, (w * keep.unsqueeze(2)).sum(1) / n
+        H = torch.bmm(((y - ym.unsqueeze(1)) * keep.unsqueeze(2)).transpose(1, 2), w - wm.unsqueeze(1))
+        U, _, Vt = torch.linalg.svd(H)
+        V = Vt.transpose(1, 2)
+        D = torch.eye(3, device=dev, dtype=torch.float64).repeat(idx.numel(), 1, 1)
+        D[:, 2, 2] = torch.where(torch.det(torch.bmm(V, U.transpose(1, 2))) < 0, -1.0, 1.0)
+        R = torch.bmm(torch.bmm(V, D), U.transpose(1, 2))
+        upd = torch.eye(4, device=dev, dtype=torch.float64).repeat(idx.numel(), 1, 1)
+        upd[:, :3, :3] = R
+        upd[:, :3, 3] = wm - torch.bmm(R, ym.unsqueeze(2)).squeeze(2)
+        has = keep.sum(1) > 0          # no correspondence: the transformation stays (Open3D returns early)
+        Tn = torch.where(has.reshape(-1, 1, 1), torch.bmm(upd, T[idx]), T[idx])
+        T[idx] = Tn
+        nfit, nrm, nn_, y, w, keep = evaluate(idx, Tn)
+        stop = ((fit[idx] - nfit).abs() < relative_fitness) & ((rm[idx] - nrm).abs() < relative_rmse)
+        fit[idx], rm[idx], ncorr[idx], its[idx] = nfit, nrm, nn_, float(i + 1)
+        go = ~stop
+        idx, y, w, keep = idx[go], y[go], w[go], keep[go]
+    return RegistrationResult(T.float(), fit.float(), rm.float(), its, ncorr.float())
+
+
 def registration_icp(source, target, max_correspondence_distance=THRESHOLD, init=None,
                      max_iteration=MAX_ITERATION, relative_fitness=1e-6, relative_rmse=1e-6):
     """source[P,N,3], target[P,M,3] float32 CUDA; init: 4x4 (shared) or [P,4,4]."""
@@ -47,6 +102,9 @@ def registration_icp(source, target, max_correspondence_distance=THRESHOLD, init
     per_pair = 1 if init.dim() == 3 else 0
     if per_pair and init.shape[0] != P:
         raise RuntimeError("init must be [4,4] or [P,4,4]")
+    if max(N, M) > RESIDENT_MAX_POINTS and P > 0:
+        return _registration_icp_large(source, target, max_correspondence_distance, init,
+                                       max_iteration, relative_fitness, relative_rmse)
     T = torch.empty(P, 4, 4, device=source.device)
     stats = torch.empty(P, 4, device=source.device)
     with torch.cuda.device(source.device):

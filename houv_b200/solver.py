@@ -25,6 +25,7 @@ W_3D, W_VIEW, ALPHA = 6.0, 1.0, 0.5  # houv.py:209,222
 # When set to a list, every K3 launch appends (start_event, end_event, rows, iters, N)
 # recorded on the launching stream: bench.py derives the kernel's roofline from it.
 KERNEL_TIMING = None
+FUSED_MAX_POINTS = 2048  # csrc/pose_common.cuh kPts: both clouds of a pair live in one SM's shared memory
 # What the last solve_model_batches call did on this rank: pairs, pairs sent through the retry
 # cascade (best min_1 above 0.030 after angle_base 0), rows of its first-pass and retry launches
 # (the retry rows this rank RAN, which differ from the ones it owns when rows are dealt over ranks).
@@ -121,6 +122,78 @@ class HOUV(nn.Module):
         return src_temp, R, T
 
 
+def _pose_optimise_large(src, tgt, params, kernel, iters, angle_base, grad_scale, adam_m, adam_v,
+                         step0, lr, betas, eps, percent, w3d, wview, want_loss, want_trace,
+                         row_pair, row_base, tran_scale, tran_offset, want_tran_s, row_scale,
+                         rows_per_chunk=64):
+    """pose_optimise for clouds of more than FUSED_MAX_POINTS points, which the fused kernel cannot
+    keep resident: the reference's own scheme (houv.py:94-126 -- torch forward, Predict_loss terms,
+    autograd, Adam) on the device over THIS package's Chamfer operator (K1 / K2 take any size,
+    chamfer3D.cu:15,22 grid-stride semantics), rows in chunks.  Same contract as the fused path:
+    per-row pair / angle_base / gradient scale, float32 or float64 state updated in place, resume
+    through step0 / adam_m / adam_v, results of the LAST forward.  The k-th-rank tie rule is
+    torch.topk's here."""
+    from . import loss as L
+    dev, rows = src.device, params.shape[0]
+    P, N, _ = src.shape
+    if row_pair is None:
+        row_pair = torch.arange(P, device=dev, dtype=torch.int32).repeat_interleave(kernel)
+    pair = row_pair.long()
+    base = (row_base.float() if row_base is not None
+            else torch.full((rows,), float(angle_base), device=dev))
+    scale = (row_scale if row_scale is not None
+             else torch.full((rows,), float(grad_scale), device=dev))
+    pi = torch.acos(torch.zeros(1)).item() * 2                      # float32 pi, houv.py:19
+    m = adam_m if adam_m is not None else torch.zeros_like(params)
+    v = adam_v if adam_v is not None else torch.zeros_like(params)
+    min1 = torch.empty(rows, device=dev)
+    R_out, T_out = torch.empty(rows, 3, 3, device=dev), torch.empty(rows, 3, device=dev)
+    loss_out = torch.empty(rows, device=dev) if want_loss else None
+    ts_out = torch.empty(rows, device=dev) if want_tran_s else None
+    trace = torch.empty(iters, rows, 2, device=dev) if want_trace else None
+    eye = torch.eye(3, device=dev)
+    for it in range(iters):
+        grad = torch.zeros(rows, 8, device=dev)
+        for lo in range(0, rows, rows_per_chunk):
+            sl = slice(lo, min(lo + rows_per_chunk, rows))
+            p = params[sl].float().detach().requires_grad_(True)    # float64 leaves feed float32 (train_utils.py:397-401)
+            s_rows, t_rows = src[pair[sl]], tgt[pair[sl]]
+            V = p[:, 0:3] / torch.sqrt((p[:, 0:3] * p[:, 0:3]).sum(1, keepdim=True))
+            ang = torch.sin(p[:, 3:4] * pi) * pi / 8 + pi / 8 + base[sl].unsqueeze(1) * pi / 4
+            A = torch.zeros(p.shape[0], 3, 3, device=dev)
+            A[:, 0, 1], A[:, 0, 2], A[:, 1, 0] = -V[:, 2], V[:, 1], V[:, 2]
+            A[:, 1, 2], A[:, 2, 0], A[:, 2, 1] = -V[:, 0], -V[:, 1], V[:, 0]
+            Rm = eye + torch.sin(ang).unsqueeze(2) * A + (1 - torch.cos(ang)).unsqueeze(2) * torch.bmm(A, A)
+            tsz = torch.sin(p[:, 7:8] * pi) * tran_scale + tran_offset
+            Tv = (p[:, 4:7] / torch.sqrt((p[:, 4:7] * p[:, 4:7]).sum(1, keepdim=True)) * tsz).unsqueeze(1)
+            y = torch.bmm(s_rows, Rm.transpose(1, 2)) + Tv
+            cd_t, cd_p = L.calc_cd_percent(y, t_rows, percent=percent)
+            min_1 = torch.min(torch.stack([cd_t, cd_p], 1), dim=1).values
+            loss = min_1 * w3d
+            if wview != 0.0:
+                for dim in range(3):
+                    a, b = L.loss_view(y, t_rows, dim=dim)
+                    loss = loss + wview * torch.min(torch.stack([a, b], 1), dim=1).values
+            (loss * scale[sl]).sum().backward()
+            grad[sl] = p.grad
+            if trace is not None:
+                trace[it, sl, 0], trace[it, sl, 1] = loss.detach(), min_1.detach()
+            if it == iters - 1:
+                min1[sl], R_out[sl], T_out[sl] = min_1.detach(), Rm.detach(), Tv.detach()[:, 0]
+                if loss_out is not None:
+                    loss_out[sl] = loss.detach()
+                if ts_out is not None:
+                    ts_out[sl] = tsz.detach()[:, 0]
+        # torch.optim.Adam (no weight decay / amsgrad), in the precision of the state
+        t = step0 + it + 1
+        g = grad.to(params.dtype)
+        m.mul_(betas[0]).add_(g, alpha=1 - betas[0])
+        v.mul_(betas[1]).addcmul_(g, g, value=1 - betas[1])
+        denom = v.sqrt() / (1 - betas[1] ** t) ** 0.5 + eps
+        params.addcdiv_(m, denom, value=-lr / (1 - betas[0] ** t))
+    return dict(min_1=min1, R=R_out, T=T_out, loss=loss_out, trace=trace, tran_s=ts_out)
+
+
 def pose_optimise(src, tgt, params, kernel, iters, angle_base=0, grad_scale=None,
                   adam_m=None, adam_v=None, step0=0, lr=ADAM_LR, betas=ADAM_BETAS, eps=ADAM_EPS,
                   percent=ALPHA, w3d=W_3D, wview=W_VIEW, want_loss=False, want_trace=False,
@@ -171,6 +244,18 @@ def pose_optimise(src, tgt, params, kernel, iters, angle_base=0, grad_scale=None
     ptr = lambda x: 0 if x is None else x.data_ptr()
     if grad_scale is None:
         grad_scale = 1.0 / rows  # rmse_loss.mean() over every row of the batch, houv.py:124
+    if row_scale is not None and (row_scale.dtype != torch.float32 or not row_scale.is_cuda
+                                  or row_scale.numel() != rows or not row_scale.is_contiguous()):
+        raise RuntimeError("row_scale must be a contiguous float32 CUDA tensor of [rows]")
+    if max(N, M) > FUSED_MAX_POINTS:
+        # the reference's loop takes any cloud size (chamfer3D.cu:15,22); so does this call
+        if N != M:
+            raise RuntimeError("src and tgt must hold the same number of points "
+                               "(calc_cd_percent trims both lists to k = N*percent)")
+        return _pose_optimise_large(src, tgt, params, kernel, iters, angle_base, grad_scale, adam_m,
+                                    adam_v, step0, lr, betas, eps, percent, w3d, wview, want_loss,
+                                    want_trace, row_pair, row_base, tran_scale, tran_offset,
+                                    want_tran_s, row_scale)
     q = _lib.HouvPoseProblem()
     q.src, q.tgt, q.P, q.N, q.M, q.K = src.data_ptr(), tgt.data_ptr(), P, N, M, kernel
     if f64:
@@ -183,9 +268,6 @@ def pose_optimise(src, tgt, params, kernel, iters, angle_base=0, grad_scale=None
     q.tran_scale, q.tran_offset = tran_scale, tran_offset
     q.min1_out, q.loss_out, q.R_out, q.T_out = min1.data_ptr(), ptr(loss), R.data_ptr(), T.data_ptr()
     q.tran_s_out, q.trace = ptr(tran_s), ptr(trace)
-    if row_scale is not None and (row_scale.dtype != torch.float32 or not row_scale.is_cuda
-                                  or row_scale.numel() != rows or not row_scale.is_contiguous()):
-        raise RuntimeError("row_scale must be a contiguous float32 CUDA tensor of [rows]")
     q.row_pair, q.row_base, q.rows = ptr(row_pair), ptr(row_base), rows
     q.row_scale = ptr(row_scale)
     timing = KERNEL_TIMING

@@ -189,9 +189,8 @@ def test_bad_arguments_raise():
         solver.pose_optimise(src.cuda(), tgt.cuda()[:, :200].contiguous(), p, KERNEL, 1)  # N != M
     with pytest.raises(RuntimeError):
         solver.pose_optimise(src, tgt, p, KERNEL, 1)  # CPU tensors
-    big = torch.rand(1, 4096, 3).cuda()
     with pytest.raises(RuntimeError):
-        solver.pose_optimise(big, big, p, KERNEL, 1)  # > 2048 points
+        solver.pose_optimise(src.cuda(), tgt.cuda(), p, KERNEL, 0)  # no iteration: nothing to return
 
 
 @pytest.mark.parametrize("n,iters,kw", [(256, 6, {}), (333, 4, {}), (2048, 3, {}),
@@ -281,3 +280,57 @@ def test_duo_row_layouts(pose_variant):
     for other in res[1:]:
         for a, b in zip(res[0], other):
             assert torch.equal(a, b)
+
+
+@pytest.mark.parametrize("n", [4096, 3000])
+def test_clouds_above_2048_points(pose_variant, n):
+    """The reference's loop takes any cloud size (chamfer3D.cu:15,22).  Above 2048 points the two
+    clouds of a pair no longer fit one SM, and pose_optimise runs the reference's scheme on the
+    device over the K1 / K2 operator instead of the fused kernel (solver._pose_optimise_large):
+    forward values, all 8 gradients, the Adam step and a resumed second call against the oracle."""
+    if pose_variant != 20:
+        pytest.skip("independent of the fused kernel")
+    from houv_b200 import solver
+    src, tgt, _ = _pairs(41, 1, n=n)
+    trace, (l, R, T), net = _oracle_trace(src, tgt, 2)
+    out, params, m, v = _gpu_run(src, tgt, 1)
+    assert _rel(out["trace"][0, :, 0].cpu(), trace[0]["loss"]) < 1e-5
+    assert _rel(out["trace"][0, :, 1].cpu(), trace[0]["min_1"]) < 1e-5
+    g_gpu = (m / 0.1).cpu().numpy().astype(np.float64)
+    g_ref = torch.cat(trace[0]["grads"], dim=1).numpy().astype(np.float64)
+    norm = np.linalg.norm(g_ref, axis=1, keepdims=True)
+    assert (np.abs(g_gpu - g_ref) / np.maximum(norm, 1e-30)).max() < 1e-4
+    more = solver.pose_optimise(src.cuda(), tgt.cuda(), params, KERNEL, 1, adam_m=m, adam_v=v,
+                                step0=1, want_trace=True, want_loss=True)
+    assert _rel(more["trace"][0, :, 0].cpu(), trace[1]["loss"]) < 1e-4
+    assert _rel(more["min_1"].cpu(), l.detach().reshape(-1)) < 1e-4
+    assert np.abs(more["R"].cpu().numpy() - R.detach().reshape(-1, 3, 3).numpy()).max() < 1e-5
+    assert np.abs(more["T"].cpu().numpy() - T.detach().reshape(-1, 3).numpy()).max() < 1e-5
+
+
+def test_large_cloud_path_agrees_with_fused_kernel(pose_variant, monkeypatch):
+    """Same call, both paths, at a size both take (2048 points, per-row pair / angle_base / scale)."""
+    if pose_variant != 20:
+        pytest.skip("compares the unfused large-cloud path with the default fused kernel")
+    from houv_b200 import solver
+    src, tgt, _ = _pairs(43, 2, n=2048)
+    rows = 40
+    g = torch.Generator().manual_seed(2)
+    row_pair = torch.tensor([0] * 22 + [1] * 18, dtype=torch.int32).cuda()
+    row_base = torch.randint(0, 4, (rows,), generator=g, dtype=torch.int32).cuda()
+    row_scale = ((torch.rand(rows, generator=g) + 0.5) / rows).cuda()
+    init = torch.from_numpy(solver.initial_parameters(64))[:rows].contiguous()
+    res = []
+    for limit in (2048, 0):
+        monkeypatch.setattr(solver, "FUSED_MAX_POINTS", limit)
+        params = init.clone().cuda()
+        m, v = torch.zeros(rows, 8).cuda(), torch.zeros(rows, 8).cuda()
+        out = solver.pose_optimise(src.cuda(), tgt.cuda(), params, KERNEL, 3, row_pair=row_pair,
+                                   row_base=row_base, row_scale=row_scale, adam_m=m, adam_v=v,
+                                   want_trace=True, want_loss=True, want_tran_s=True)
+        res.append((out, params, m))
+    (a, pa, ma), (b, pb, mb) = res
+    assert _rel(b["trace"][0].cpu(), a["trace"][0].cpu()) < 1e-5
+    assert _rel(b["trace"][2].cpu(), a["trace"][2].cpu()) < 2e-4
+    assert _rel(b["tran_s"].cpu(), a["tran_s"].cpu()) < 1e-5
+    assert np.abs((pb - pa).cpu().numpy()).max() < 1e-4

@@ -277,3 +277,38 @@ def test_balanced_retry_equals_local_retry():
         dist.destroy_process_group()
     assert torch.equal(local, dealt) and torch.equal(none_l, none_d)
     assert tuple(empty.shape) == (0, 4, 4)  # a rank without pairs still joins the exchange
+
+
+@pytest.mark.gpu
+def test_icp_clouds_above_2048_points(monkeypatch):
+    """Open3D's registration_icp takes any cloud size; above 2048 points the resident kernel cannot
+    hold a pair and registration_icp runs the same loop on the device over K1's directed search
+    (icp._registration_icp_large).  Against the float64 restatement (unpinned, like the kernel), and
+    against the resident kernel on a size both take."""
+    from houv_b200 import icp
+    rng = np.random.RandomState(5)
+    P, N = 2, 2500
+    tgt = (rng.rand(P, N, 3) - 0.5).astype(np.float32)
+    src = np.empty_like(tgt)
+    for p in range(P):
+        Rp, _ = synth.random_rotation(rng, np.deg2rad(3.0))
+        tp = rng.randn(3) * 0.003
+        src[p] = ((tgt[p] - tp) @ Rp).astype(np.float32)
+    reg = icp.registration_icp(torch.from_numpy(src).cuda(), torch.from_numpy(tgt).cuda(), 0.04,
+                               np.eye(4, dtype=np.float32), 40)
+    T = reg.transformation.cpu().numpy()
+    for p in range(P):
+        To, fit, rm, it = oh.icp_point_to_point(src[p], tgt[p], 0.04, np.eye(4), 40)
+        assert _geodesic_rad(T[p:p + 1, :3, :3], To[None, :3, :3]).max() < 1e-4
+        assert np.abs(T[p, :3, 3] - To[:3, 3]).max() < 1e-5
+        assert abs(float(reg.fitness[p]) - fit) < 1e-6 and abs(float(reg.inlier_rmse[p]) - rm) < 1e-5
+        assert int(reg.iterations[p]) == it
+    # both paths on 1500 points
+    s, t = torch.from_numpy(src[:, :1500].copy()).cuda(), torch.from_numpy(tgt[:, :1500].copy()).cuda()
+    a = icp.registration_icp(s, t, 0.05, np.eye(4, dtype=np.float32), 60)
+    monkeypatch.setattr(icp, "RESIDENT_MAX_POINTS", 0)
+    b = icp.registration_icp(s, t, 0.05, np.eye(4, dtype=np.float32), 60)
+    assert _geodesic_rad(a.transformation[:, :3, :3].cpu().numpy(),
+                         b.transformation[:, :3, :3].cpu().numpy()).max() < 1e-4
+    assert (a.transformation[:, :3, 3] - b.transformation[:, :3, 3]).abs().max() < 1e-5
+    assert (a.fitness - b.fitness).abs().max() < 1e-6
