@@ -45,6 +45,8 @@ _SIGNATURES = {
     "houv_emd_backward": [_vp, _vp, _vp, _vp, _ci, _ci, _vp, _vp],
     "houv_idam_step": [_vp, _vp, _vp, _ci, _vp, _ci, _ci, _ci, _vp, _vp, _vp, _vp, _vp, _vp, _vp],
     "houv_chamfer3d_backward_assign": [_vp, _vp, _vp, _vp, _vp, _vp, _ci, _ci, _ci, _vp, _vp, _vp],
+    "houv_chamfer3d_backward_deterministic": [_vp, _vp, _vp, _vp, _vp, _vp, _ci, _ci, _ci, _vp, _vp,
+                                              _ci, _vp],
     "houv_kabsch": [_vp, _vp, _vp, _ci, _ci, _vp, _vp, _vp],
     "houv_icp": [_vp, _vp, _ci, _ci, _ci, _vp, _ci, _cf, _ci, ctypes.c_double, ctypes.c_double,
                  _vp, _vp, _vp],

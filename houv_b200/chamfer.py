@@ -17,6 +17,9 @@ from torch.autograd import Function
 from . import _lib
 
 
+DETERMINISTIC_MAX_POINTS = 2048  # csrc/chamfer_bwd.cu kGMax
+
+
 class _Chamfer3DModule:
     """Object with the reference pybind module's two entry points
     (chamfer_cuda.cpp:30-33): forward/backward on caller-allocated tensors,
@@ -47,6 +50,25 @@ class _Chamfer3DModule:
         B, N, _ = xyz1.shape
         M = xyz2.shape[1]
         lib = _lib.load()
+        if torch.are_deterministic_algorithms_enabled():
+            # torch.use_deterministic_algorithms(True): the gather-side kernel (no float atomics,
+            # bit-identical to a sequential run of the reference kernels); clouds up to 2048 points
+            if max(N, M) > DETERMINISTIC_MAX_POINTS:
+                msg = ("chamfer_3D.backward has no deterministic kernel for clouds above %d points "
+                       "(float atomics, like the reference)" % DETERMINISTIC_MAX_POINTS)
+                if not torch.is_deterministic_algorithms_warn_only_enabled():
+                    raise RuntimeError(msg)
+                import warnings
+                warnings.warn(msg)
+            else:
+                with torch.cuda.device(xyz1.device):
+                    rc = lib.houv_chamfer3d_backward_deterministic(
+                        xyz1.data_ptr(), xyz2.data_ptr(), graddist1.data_ptr(), graddist2.data_ptr(),
+                        idx1.data_ptr(), idx2.data_ptr(), B, N, M, gradxyz1.data_ptr(),
+                        gradxyz2.data_ptr(), 1 if assign else 0, _lib.stream_ptr())
+                _lib.check(rc, "houv_chamfer3d_backward_deterministic")
+                _lib.count_launches(1)
+                return 1
         fn = lib.houv_chamfer3d_backward_assign if assign else lib.houv_chamfer3d_backward
         with torch.cuda.device(xyz1.device):
             rc = fn(xyz1.data_ptr(), xyz2.data_ptr(), graddist1.data_ptr(), graddist2.data_ptr(),

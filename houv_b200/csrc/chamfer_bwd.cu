@@ -196,13 +196,159 @@ __global__ void __launch_bounds__(kResThreads, 2) grad_resident_kernel(const Gra
     }
 }
 
+// ---------------------------------------------------------------------------------------------
+// Deterministic form: gather-side accumulation through the inverse index.
+//
+// The reference adds colliding scatters with float atomics in whatever order the GPU schedules them
+// (chamfer3D.cu:166-171; registration/README.md:82-90 concedes the run-to-run drift).  Here one CTA
+// owns one batch element, inverts idx1 / idx2 in shared memory (counting sort: integer atomics for
+// the bucket sizes, block scan, fill, then every bucket sorted by point index) and every gradient
+// row is summed by ONE thread in the order a single-thread run of the reference kernels would use:
+//   gradxyz1[i] = (0 + own term of direction 1) - scattered terms of direction 2, ascending j
+//   gradxyz2[k] = (0 - scattered terms of direction 1, ascending i) + own term of direction 2
+// -- bit-identical to oracle/chamfer_oracle.c::oracle_chamfer_backward_f32 (= the reference kernel
+// bodies run by one host thread), run to run and GPU to GPU.  No floating-point atomics anywhere:
+// shared memory sees native integer atomics only, the rows leave with plain coalesced stores.
+// Clouds up to 2048 points (indices held as 16-bit), 104 KB of shared memory, two CTAs per SM.
+constexpr int kGThreads = 512;
+constexpr int kGMax = 2048;      // points per cloud
+constexpr int kGSortMax = 32;    // buckets up to this size are sorted in place; larger ones rescan idx
+
+struct GatherSmem {
+    float s1[kGMax * 3], s2[kGMax * 3];   // the two clouds (AoS)
+    float w1[kGMax], w2[kGMax];           // 2 * graddist
+    unsigned short ix1[kGMax], ix2[kGMax];
+    unsigned short start1[kGMax + 2], start2[kGMax + 2];  // bucket offsets (exclusive scan), +1 = end
+    unsigned short list1[kGMax], list2[kGMax];            // points grouped by the bucket they hit
+    int cnt1[kGMax], cnt2[kGMax];         // bucket sizes / fill cursors
+    int wsum[2][kGThreads / 32];
+};
+
+// exclusive scan of cnt[0..len) into start[0..len], cnt reset to 0; every thread owns 4 entries
+__device__ __forceinline__ void gather_scan(int *cnt, unsigned short *start, int len, int *wsum) {
+    const int t = threadIdx.x, base = 4 * t;
+    int c[4], s = 0;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) { c[q] = base + q < len ? cnt[base + q] : 0; s += c[q]; }
+    int incl = s;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int v = __shfl_up_sync(0xffffffffu, incl, o);
+        if ((t & 31) >= o) incl += v;
+    }
+    if ((t & 31) == 31) wsum[t >> 5] = incl;
+    __syncthreads();
+    int off = 0;
+    for (int ww = 0; ww < (t >> 5); ++ww) off += wsum[ww];
+    int run = off + incl - s;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+        if (base + q < len) { start[base + q] = (unsigned short)run; cnt[base + q] = 0; }
+        run += c[q];
+    }
+    if (t == kGThreads - 1) start[len] = (unsigned short)run;  // = number of points scattered
+}
+
+// Sum over the points of bucket [p0, p0+L) of `list` in ascending point order of
+// -w[i] * (sa[i] - b_k): the scattered terms a single-thread reference run adds to row k.
+__device__ __forceinline__ void gather_bucket(unsigned short *list, int p0, int L, const unsigned short *ix,
+                                              int n_src, int k, const float *sa, const float *w,
+                                              float bx, float by, float bz, float (&acc)[3]) {
+    auto add = [&](int i) {
+        const float g = w[i];
+        acc[0] = __fadd_rn(acc[0], -__fmul_rn(g, __fsub_rn(sa[3 * i + 0], bx)));
+        acc[1] = __fadd_rn(acc[1], -__fmul_rn(g, __fsub_rn(sa[3 * i + 1], by)));
+        acc[2] = __fadd_rn(acc[2], -__fmul_rn(g, __fsub_rn(sa[3 * i + 2], bz)));
+    };
+    if (L <= kGSortMax) {
+        for (int a = 1; a < L; ++a) {  // insertion sort: buckets hold one or two points as a rule
+            const unsigned short v = list[p0 + a];
+            int b = a - 1;
+            while (b >= 0 && list[p0 + b] > v) { list[p0 + b + 1] = list[p0 + b]; --b; }
+            list[p0 + b + 1] = v;
+        }
+        for (int a = 0; a < L; ++a) add(list[p0 + a]);
+    } else {
+        for (int i = 0; i < n_src; ++i)
+            if (ix[i] == k) add(i);
+    }
+}
+
+__global__ void __launch_bounds__(kGThreads, 2) grad_gather_kernel(const GradArgs args, int B, bool assign) {
+    extern __shared__ __align__(16) unsigned char gsm_raw[];
+    GatherSmem &S = *reinterpret_cast<GatherSmem *>(gsm_raw);
+    const int n = args.dir[0].n, m = args.dir[0].m, t = threadIdx.x;
+    for (int bi = blockIdx.x; bi < B; bi += gridDim.x) {
+        const float *gd1 = args.dir[0].gd + (long long)bi * n, *gd2 = args.dir[1].gd + (long long)bi * m;
+        const int *ix1 = args.dir[0].idx + (long long)bi * n, *ix2 = args.dir[1].idx + (long long)bi * m;
+        res_stage(S.s1, args.dir[0].a + (long long)bi * n * 3, n * 3);
+        res_stage(S.s2, args.dir[0].b + (long long)bi * m * 3, m * 3);
+        for (int i = t; i < n; i += kGThreads) {
+            S.w1[i] = __fmul_rn(__ldg(gd1 + i), 2.f);
+            S.ix1[i] = (unsigned short)__ldg(ix1 + i);
+            S.cnt2[i] = 0;
+        }
+        for (int j = t; j < m; j += kGThreads) {
+            S.w2[j] = __fmul_rn(__ldg(gd2 + j), 2.f);
+            S.ix2[j] = (unsigned short)__ldg(ix2 + j);
+            S.cnt1[j] = 0;
+        }
+        __syncthreads();
+        // bucket sizes: direction 1 scatters into the m points of cloud 2, direction 2 into cloud 1
+        for (int i = t; i < n; i += kGThreads) atomicAdd(&S.cnt1[S.ix1[i]], 1);
+        for (int j = t; j < m; j += kGThreads) atomicAdd(&S.cnt2[S.ix2[j]], 1);
+        __syncthreads();
+        gather_scan(S.cnt1, S.start1, m, S.wsum[0]);
+        gather_scan(S.cnt2, S.start2, n, S.wsum[1]);
+        __syncthreads();
+        for (int i = t; i < n; i += kGThreads) {
+            const int k = S.ix1[i];
+            S.list1[S.start1[k] + atomicAdd(&S.cnt1[k], 1)] = (unsigned short)i;
+        }
+        for (int j = t; j < m; j += kGThreads) {
+            const int k = S.ix2[j];
+            S.list2[S.start2[k] + atomicAdd(&S.cnt2[k], 1)] = (unsigned short)j;
+        }
+        __syncthreads();
+        // rows of cloud 1: own term of direction 1 first, then what direction 2 scatters, ascending
+        float *o1 = args.dir[0].ga + (long long)bi * n * 3, *o2 = args.dir[0].gb + (long long)bi * m * 3;
+        for (int i = t; i < n; i += kGThreads) {
+            const float ax = S.s1[3 * i], ay = S.s1[3 * i + 1], az = S.s1[3 * i + 2];
+            const int j = S.ix1[i];
+            const float g = S.w1[i];
+            float acc[3];
+            acc[0] = __fadd_rn(0.f, __fmul_rn(g, __fsub_rn(ax, S.s2[3 * j + 0])));
+            acc[1] = __fadd_rn(0.f, __fmul_rn(g, __fsub_rn(ay, S.s2[3 * j + 1])));
+            acc[2] = __fadd_rn(0.f, __fmul_rn(g, __fsub_rn(az, S.s2[3 * j + 2])));
+            gather_bucket(S.list2, S.start2[i], S.cnt2[i], S.ix2, m, i, S.s2, S.w2, ax, ay, az, acc);
+#pragma unroll
+            for (int c = 0; c < 3; ++c) o1[3 * i + c] = assign ? acc[c] : __fadd_rn(o1[3 * i + c], acc[c]);
+        }
+        // rows of cloud 2: what direction 1 scatters (ascending), then the own term of direction 2
+        for (int k = t; k < m; k += kGThreads) {
+            const float bx = S.s2[3 * k], by = S.s2[3 * k + 1], bz = S.s2[3 * k + 2];
+            float acc[3] = {0.f, 0.f, 0.f};
+            gather_bucket(S.list1, S.start1[k], S.cnt1[k], S.ix1, n, k, S.s1, S.w1, bx, by, bz, acc);
+            const int i = S.ix2[k];
+            const float g = S.w2[k];
+            acc[0] = __fadd_rn(acc[0], __fmul_rn(g, __fsub_rn(bx, S.s1[3 * i + 0])));
+            acc[1] = __fadd_rn(acc[1], __fmul_rn(g, __fsub_rn(by, S.s1[3 * i + 1])));
+            acc[2] = __fadd_rn(acc[2], __fmul_rn(g, __fsub_rn(bz, S.s1[3 * i + 2])));
+#pragma unroll
+            for (int c = 0; c < 3; ++c) o2[3 * k + c] = assign ? acc[c] : __fadd_rn(o2[3 * k + c], acc[c]);
+        }
+        __syncthreads();
+    }
+}
+
 }  // namespace houv
 
 using namespace houv;
 
 static int backward_impl(const float *xyz1, const float *xyz2, const float *graddist1,
                          const float *graddist2, const int *idx1, const int *idx2, int B, int N,
-                         int M, float *gradxyz1, float *gradxyz2, bool assign, void *stream) {
+                         int M, float *gradxyz1, float *gradxyz2, bool assign, void *stream,
+                         bool deterministic = false) {
     if (B < 0 || N < 0 || M < 0) return HOUV_E_BADARG;
     if (assign && B > 0) {  // an empty partner cloud leaves a zero gradient
         if ((N > 0 && !gradxyz1) || (M > 0 && !gradxyz2)) return HOUV_E_BADARG;
@@ -229,7 +375,20 @@ static int backward_impl(const float *xyz1, const float *xyz2, const float *grad
     const size_t res_bytes = 2 * sizeof(float) * ((((size_t)N * 3 + 3) & ~(size_t)3) +
                                                   (((size_t)M * 3 + 3) & ~(size_t)3));
     const bool fits = res_bytes <= 200 * 1024;
-    if (fits && (forced >= 1 || (forced < 0 && B >= 148))) {
+    // The deterministic gather kernel (clouds up to 2048 points) on request -- the _deterministic
+    // entry point or HOUV_K2_VARIANT=2; it costs ~1.5x the float-atomics kernels (measured, B200:
+    // 6400 x 2048^2 447 us against 290 us resident; 32 x 2048^2 20.5 us against 13.3 us streaming).
+    // HOUV_K2_VARIANT: 1 = the float-atomics resident kernel, 0 = streaming.
+    if (deterministic && (N > kGMax || M > kGMax)) return HOUV_E_TOOBIG;
+    if (N <= kGMax && M <= kGMax && (forced == 2 || (forced < 0 && deterministic))) {
+        int grid = 2 * 148;
+        if (grid > B) grid = B;
+        static unsigned long long gsmem_set = 0;
+        if (int e = ensure_dyn_smem(grad_gather_kernel, (int)sizeof(GatherSmem), gsmem_set)) return e;
+        grad_gather_kernel<<<grid, kGThreads, sizeof(GatherSmem), (cudaStream_t)stream>>>(a, B, assign);
+        return check_launch();
+    }
+    if (fits && (forced == 1 || (forced < 0 && B >= 148))) {
         const int per_sm = (int)((227 * 1024) / (res_bytes + 1024));
         int grid = 148 * (per_sm < 1 ? 1 : per_sm > 2 ? 2 : per_sm);  // registers allow 2 x 512 threads
         if (grid > B) grid = B;
@@ -257,6 +416,15 @@ extern "C" int houv_chamfer3d_backward(const float *xyz1, const float *xyz2,
                                        float *gradxyz1, float *gradxyz2, void *stream) {
     return backward_impl(xyz1, xyz2, graddist1, graddist2, idx1, idx2, B, N, M, gradxyz1, gradxyz2,
                          false, stream);
+}
+
+extern "C" int houv_chamfer3d_backward_deterministic(const float *xyz1, const float *xyz2,
+                                                     const float *graddist1, const float *graddist2,
+                                                     const int *idx1, const int *idx2, int B, int N,
+                                                     int M, float *gradxyz1, float *gradxyz2,
+                                                     int assign, void *stream) {
+    return backward_impl(xyz1, xyz2, graddist1, graddist2, idx1, idx2, B, N, M, gradxyz1, gradxyz2,
+                         assign != 0, stream, true);
 }
 
 extern "C" int houv_chamfer3d_backward_assign(const float *xyz1, const float *xyz2,

@@ -91,6 +91,19 @@ int houv_chamfer3d_backward_assign(const float *xyz1, const float *xyz2, const f
                                    const float *graddist2, const int *idx1, const int *idx2, int B,
                                    int N, int M, float *gradxyz1, float *gradxyz2, void *stream);
 
+/* The same gradient, DETERMINISTIC: every row is summed by one thread in the order a single-thread
+ * run of the reference kernels adds it (direction 1 then direction 2, ascending point index), so
+ * the result is identical run to run and bit-identical to the reference kernel bodies executed
+ * sequentially (oracle/chamfer_oracle.c) -- the reference's float atomics are order-dependent
+ * (chamfer3D.cu:166-171, registration/README.md:82-90).  assign != 0 writes the buffers, 0 adds
+ * into them.  Clouds up to 2048 points (HOUV_E_TOOBIG above); ~1.5x the time of the default.
+ * The Python layer calls this under torch.use_deterministic_algorithms(True). */
+int houv_chamfer3d_backward_deterministic(const float *xyz1, const float *xyz2,
+                                          const float *graddist1, const float *graddist2,
+                                          const int *idx1, const int *idx2, int B, int N, int M,
+                                          float *gradxyz1, float *gradxyz2, int assign,
+                                          void *stream);
+
 /* Epilogue of calc_cd + fscore (model_utils_completion.py:69-80, utils/metrics/CD/fscore.py:3-16)
  * on the outputs of a Chamfer forward: cd_p[B] = (mean sqrt dist1 + mean sqrt dist2)/2,
  * cd_t[B] = mean dist1 + mean dist2, f1[B] (or NULL) = F-score at `threshold` (1e-4 in the

@@ -168,12 +168,13 @@ def test_autograd_backward_vs_float64_oracle(shape):
     assert _grad_close(t1.grad.cpu().numpy(), h1) and _grad_close(t2.grad.cpu().numpy(), h2)
 
 
-@pytest.mark.parametrize("k2", ["0", "1"], ids=["k2-streaming", "k2-resident"])
+@pytest.mark.parametrize("k2", ["0", "1", "2"], ids=["k2-streaming", "k2-resident", "k2-gather"])
 @pytest.mark.parametrize("shape", [(3, 7, 13), (5, 1001, 999), (2, 1, 1), (150, 2048, 2048),
                                    (3, 3000, 5500)])
 def test_backward_both_kernels_vs_float64_oracle(shape, k2, monkeypatch):
-    """The streaming scatter kernel and the batch-element-resident one (csrc/chamfer_bwd.cu) give the
-    reference's gradient (chamfer3D.cu:155-195) on ragged, odd-sized and full-size clouds; buffers
+    """The streaming scatter kernel, the batch-element-resident one and the deterministic gather
+    kernel (csrc/chamfer_bwd.cu; the last for clouds up to 2048 points, else the call falls through
+    to the streaming one) give the reference's gradient (chamfer3D.cu:155-195) on ragged, odd-sized and full-size clouds; buffers
     that arrive non-zero are added into by both."""
     from houv_b200.chamfer import chamfer_3D
     monkeypatch.setenv("HOUV_K2_VARIANT", k2)
@@ -256,3 +257,49 @@ def test_extreme_finite_inputs(n, m):
     x1[1, n - 1] = [3.4e38, 3.4e38, 3.4e38]       # every distance from here is +inf -> idx 0
     _check_fwd(x1, x2)
     _check_fwd(x2, x1)
+
+
+@pytest.mark.parametrize("shape", [(3, 7, 13), (5, 1001, 999), (2, 1, 1), (40, 2048, 2048), (4, 2048, 300)])
+def test_backward_is_deterministic_and_bit_exact(shape):
+    """Under torch.use_deterministic_algorithms(True) clouds up to 2048 points take the gather-side
+    kernel (houv_chamfer3d_backward_deterministic): every gradient row is summed by one thread in
+    the order a single-thread run of the reference kernels adds it (chamfer3D.cu:155-174, direction 1
+    then direction 2, ascending point index) -- bit-identical to oracle_chamfer_backward_f32 = the
+    reference kernel bodies on one host thread, and identical run to run (the reference's own float
+    atomics are not: registration/README.md:82-90).  Many-to-one correspondences (buckets beyond the
+    in-place sort: a far-away cloud maps to a handful of targets) included."""
+    from houv_b200.chamfer import chamfer_3D
+    b, n, m = shape
+    rng = np.random.RandomState(n * 7 + m)
+    x1 = rng.rand(b, n, 3).astype(np.float32)
+    x2 = rng.rand(b, m, 3).astype(np.float32)
+    x2[0] += 3.0  # element 0: every point of cloud 1 hits one of a few points of cloud 2
+    w1 = rng.randn(b, n).astype(np.float32)
+    w2 = rng.randn(b, m).astype(np.float32)
+    t1, t2 = _dev(x1), _dev(x2)
+    d1 = torch.empty(b, n, device="cuda"); d2 = torch.empty(b, m, device="cuda")
+    i1 = torch.empty(b, n, device="cuda", dtype=torch.int32)
+    i2 = torch.empty(b, m, device="cuda", dtype=torch.int32)
+    chamfer_3D.forward(t1, t2, d1, d2, i1, i2)
+    h1, h2 = oc.chamfer_backward(x1, x2, w1, w2, i1.cpu().numpy(), i2.cpu().numpy(), f64=False)
+    was = torch.are_deterministic_algorithms_enabled()
+    torch.use_deterministic_algorithms(True)
+    try:
+        runs = []
+        for _ in range(2):
+            g1 = torch.full_like(t1, float("nan")); g2 = torch.full_like(t2, float("nan"))
+            chamfer_3D.backward(t1, t2, g1, g2, _dev(w1), _dev(w2), i1, i2, assign=True)
+            runs.append((g1.cpu().numpy(), g2.cpu().numpy()))
+        assert np.array_equal(runs[0][0], h1) and np.array_equal(runs[0][1], h2)
+        assert np.array_equal(runs[0][0], runs[1][0]) and np.array_equal(runs[0][1], runs[1][1])
+        # the accumulate entry point (the reference's contract) on zero-filled buffers: the same bits
+        g1, g2 = torch.zeros_like(t1), torch.zeros_like(t2)
+        chamfer_3D.backward(t1, t2, g1, g2, _dev(w1), _dev(w2), i1, i2)
+        assert np.array_equal(g1.cpu().numpy(), h1) and np.array_equal(g2.cpu().numpy(), h2)
+        big = torch.rand(1, 2100, 3, device="cuda")
+        ib = torch.zeros(1, 2100, device="cuda", dtype=torch.int32)
+        zb = torch.zeros(1, 2100, device="cuda")
+        with pytest.raises(RuntimeError):  # like torch ops without a deterministic implementation
+            chamfer_3D.backward(big, big, torch.zeros_like(big), torch.zeros_like(big), zb, zb, ib, ib)
+    finally:
+        torch.use_deterministic_algorithms(was)
