@@ -36,6 +36,7 @@ class HouvPoseProblem(ctypes.Structure):
 # name -> argtypes; every entry point returns int (0 = ok) unless noted
 _SIGNATURES = {
     "houv_chamfer3d_forward": [_vp, _vp, _ci, _ci, _ci, _vp, _vp, _vp, _vp, _vp],
+    "houv_chamfer3d_forward_static": [_vp, _vp, _ci, _ci, _ci, _vp, _vp, _vp, _vp, _vp],
     "houv_chamfer3d_forward_ws": [_vp, _vp, _ci, _ci, _ci, _vp, _vp, _vp, _vp, _vp,
                                   ctypes.c_size_t, _vp],
     "houv_cd_reduce": [_vp, _vp, _ci, _ci, _ci, _cf, _vp, _vp, _vp, _vp],
@@ -60,7 +61,7 @@ _SIGNATURES = {
 }
 
 EXPORTS = tuple(_SIGNATURES) + ("houv_version", "houv_chamfer3d_workspace_bytes",
-                                   "houv_emd_workspace_bytes")
+                                "houv_chamfer3d_static_scratch_bytes", "houv_emd_workspace_bytes")
 
 
 def lib_path():
@@ -77,6 +78,8 @@ def load():
             fn = getattr(lib, name)
             fn.argtypes = args
             fn.restype = _ci
+        lib.houv_chamfer3d_static_scratch_bytes.restype = ctypes.c_size_t
+        lib.houv_chamfer3d_static_scratch_bytes.argtypes = []
         lib.houv_chamfer3d_workspace_bytes.restype = ctypes.c_size_t
         lib.houv_chamfer3d_workspace_bytes.argtypes = [_ci, _ci, _ci]
         lib.houv_emd_workspace_bytes.restype = ctypes.c_size_t

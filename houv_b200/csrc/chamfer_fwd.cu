@@ -281,3 +281,48 @@ extern "C" int houv_chamfer3d_forward(const float *xyz1, const float *xyz2, int 
     return houv_chamfer3d_forward_ws(xyz1, xyz2, B, N, M, dist1, dist2, idx1, idx2, nullptr, 0,
                                      stream);
 }
+
+// ---------------------------------------------------------------------------------------------
+// houv_chamfer3d_forward_static: houv_chamfer3d_forward_ws for callers that cannot allocate
+// (CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).  No counterpart in
+// the reference.  The scratch the symmetric kernel
+// needs (64-bit column keys / row-key planes) lives in the file-scope device array below: 8 MiB,
+// held by every GPU that loads the library until the process exits.  This call allocates nothing
+// (no cudaMalloc / cudaFree / allocating library routine); a problem whose scratch would exceed the
+// array is rejected with HOUV_E_SCRATCH before anything is launched.
+//
+// In HOST code `g_static_scratch` is only a stand-in for the symbol, not a device address: the
+// address is taken once per device, with that device current, by cudaGetSymbolAddress, and that
+// pointer is what the kernels get.
+//
+// Every call shares the one array and finds the previous call's contents in it.  Nothing has to
+// start at zero for the caller's sake: the launcher re-initialises the column keys it combines
+// with atomicMin (cudaMemsetAsync 0xff on the call's stream) and every row-key plane is written
+// whole before it is read.  Calls that OVERLAP on the GPU (two streams, two host threads on one
+// device) race on the array: serialise them, or use houv_chamfer3d_forward_ws with one workspace
+// per stream.
+static __device__ __align__(256) unsigned long long g_static_scratch[HOUV_STATIC_SCRATCH_BYTES / 8];
+
+extern "C" size_t houv_chamfer3d_static_scratch_bytes(void) { return HOUV_STATIC_SCRATCH_BYTES; }
+
+extern "C" int houv_chamfer3d_forward_static(const float *xyz1, const float *xyz2, int B, int N,
+                                             int M, float *dist1, float *dist2, int *idx1,
+                                             int *idx2, void *stream) {
+    if (int e = check_sizes(B, N, M)) return e;
+    const size_t need = houv_chamfer3d_workspace_bytes(B, N, M);
+    if (need > (size_t)HOUV_STATIC_SCRATCH_BYTES) return HOUV_E_SCRATCH;
+    static void *scratch_of_device[64] = {nullptr};  // device address of the array, per device
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return (int)e;
+    if (dev < 0 || dev >= 64) return HOUV_E_BADARG;
+    void *ptr = scratch_of_device[dev];
+    if (!ptr) {
+        e = cudaGetSymbolAddress(&ptr, g_static_scratch);  // `dev` is current: its copy of the array
+        if (e != cudaSuccess) return (int)e;
+        if (!ptr) return HOUV_E_BADARG;
+        scratch_of_device[dev] = ptr;
+    }
+    return houv_chamfer3d_forward_ws(xyz1, xyz2, B, N, M, dist1, dist2, idx1, idx2, ptr,
+                                     (size_t)HOUV_STATIC_SCRATCH_BYTES, stream);
+}

@@ -36,6 +36,9 @@ extern "C" {
 
 #define HOUV_E_BADARG 100001 /* null pointer / negative size */
 #define HOUV_E_TOOBIG 100002 /* B*N*3 or B*M*3 would overflow the index math */
+#define HOUV_E_SCRATCH 100003 /* houv_chamfer3d_forward_static: the problem needs more scratch than
+                                 HOUV_STATIC_SCRATCH_BYTES (use houv_chamfer3d_forward_ws) */
+#define HOUV_STATIC_SCRATCH_BYTES (8u << 20) /* size of the library's built-in scratch array */
 
 /* Library identification, e.g. "houv_b200 0.1 sm_100a". */
 const char *houv_version(void);
@@ -68,6 +71,22 @@ size_t houv_chamfer3d_workspace_bytes(int B, int N, int M);
 int houv_chamfer3d_forward_ws(const float *xyz1, const float *xyz2, int B, int N, int M,
                               float *dist1, float *dist2, int *idx1, int *idx2,
                               void *workspace, size_t workspace_bytes, void *stream);
+
+/* The same call for callers that cannot allocate (CUDA graph capture, serving loops, harnesses
+ * that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * The scratch lives in a static device array of HOUV_STATIC_SCRATCH_BYTES (8 MiB)
+ * inside the library -- every GPU that loads the library holds it until the process exits -- and
+ * the call allocates nothing (no cudaMalloc / cudaFree / allocating library routine).  Inputs
+ * and outputs are the caller's, as above; results are identical bit for bit to
+ * houv_chamfer3d_forward_ws.  A problem whose scratch (houv_chamfer3d_workspace_bytes) exceeds
+ * the array is rejected with HOUV_E_SCRATCH before anything is launched: e.g. 32 x 2048 x 2048
+ * needs 4 MiB, 64 x 16384 x 2048 1 MiB, 200 x 8192 x 8192 12.5 MiB (rejected).  All calls share
+ * the one array (it keeps the last call's contents; the library re-initialises what it must):
+ * calls that overlap on the GPU -- two streams, two host threads on one device -- RACE on it;
+ * serialise them or use houv_chamfer3d_forward_ws with a workspace per stream. */
+int houv_chamfer3d_forward_static(const float *xyz1, const float *xyz2, int B, int N, int M,
+                                  float *dist1, float *dist2, int *idx1, int *idx2, void *stream);
+size_t houv_chamfer3d_static_scratch_bytes(void);
 
 /* One directed search: query[B,N,3] against target[B,M,3] -> dist[B,N], idx[B,N]. */
 int houv_nn_search(const float *query, const float *target, int B, int N, int M,
