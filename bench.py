@@ -136,9 +136,26 @@ def cpu_houv_sample(n_iters, threads):
 
 
 def cpu_pairs_per_s(seconds, n_iters):
-    """Linear extrapolation of the sample to a full 200-iteration angle_base-0 solve of one
-    pair.  Retries (x(1+3p)) are NOT added, which flatters the CPU arm."""
+    """pairs/s of the angle_base-0 solve of one pair: measured outright when n_iters == ITERS, else
+    a linear extrapolation of the sample.  Retries (x(1+3p)) are NOT added, which flatters the CPU arm."""
     return 1.0 / (seconds * ITERS / n_iters)
+
+
+def cpu_sample_plan(cores, budget_s=30.0):
+    """How many of the 200 iterations a CPU sample runs: ALL of them when one pair fits the budget
+    (the AVX2 oracle needs ~0.09 s per iteration on 16 cores), else as many as fit."""
+    cpu_houv_sample(1, cores)                       # warm-up: library load, thread pool
+    t_it = cpu_houv_sample(3, cores) / 3.0
+    return ITERS if t_it * ITERS <= budget_s else max(10, int(budget_s / t_it))
+
+
+def cpu_sample_text(n_it, sec, cores):
+    how = ("the WHOLE angle_base-0 solve of one pair, nothing extrapolated" if n_it == ITERS else
+           "%d of %d Adam iterations, linearly extrapolated" % (n_it, ITERS))
+    return ("1 pair x %d starts x %d iterations at angle_base 0 in %.1f s = %s (2048x2048 pts, 8 directed "
+            "NN searches + backward per iteration; CPU oracle = restated houv.py in torch-CPU over the "
+            "C chamfer restatement, AVX2, %d host threads); retries not added"
+            % (KERNEL, n_it, sec, how, cores))
 
 
 def run_reference(args):
@@ -148,17 +165,12 @@ def run_reference(args):
     import torch
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
-    n_it = 60  # a bounded sample (seconds of host work per step), long enough to time steadily
-    for _ in range(args.warmup):
+    n_it = cpu_sample_plan(cores)
+    for _ in range(max(args.warmup - 1, 0)):
         cpu_houv_sample(1, cores)
     ts = [cpu_houv_sample(n_it, cores) for _ in range(args.steps)]
     sec = sum(ts) / len(ts)
     val = cpu_pairs_per_s(sec, n_it)
-    sample = ("each step = 1 pair x %d starts x %d of %d Adam iterations at angle_base 0 "
-              "(2048x2048 pts, 8 directed NN searches + backward per iteration; CPU oracle = "
-              "restated houv.py in torch-CPU over the C chamfer restatement, AVX2, all host "
-              "threads); pairs/s = 1/(t_step*%d/%d), retries not added" %
-              (KERNEL, n_it, ITERS, ITERS, n_it))
     print(json.dumps({
         "impl": "reference", "metric": "registered pairs/sec (2048-pt, HOUV full)",
         "value": val, "unit": "pairs/s", "n_gpus": args.gpus, "steps": args.steps,
@@ -166,7 +178,7 @@ def run_reference(args):
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": workload_config(args),
         "cpu_baseline": {"value": val, "unit": "pairs/s", "cores": cores, "kind": "port",
-                         "sample": sample},
+                         "sample": "each step = " + cpu_sample_text(n_it, sec, cores)},
         "e2e": {"value": val, "unit": "pairs/s", "h2d_bytes_per_step": 0,
                 "d2h_bytes_per_step": 0}}))
 
@@ -576,16 +588,11 @@ def run_ours(args):
     if world == 1 and not args.no_cpu_baseline:
         cores = os.cpu_count() or 1
         torch.set_num_threads(cores)
-        cpu_houv_sample(1, cores)
-        n_it = 60  # ~12 s of host work: the bounded sample the contract asks for (10-30 s)
+        n_it = cpu_sample_plan(cores)
         sec = cpu_houv_sample(n_it, cores)
         line["cpu_baseline"] = {
             "value": cpu_pairs_per_s(sec, n_it), "unit": "pairs/s", "cores": cores,
-            "kind": "port",
-            "sample": "1 pair x %d starts x %d of %d Adam iterations at angle_base 0 in %.1f s "
-                      "(CPU oracle: restated houv.py in torch-CPU over the C chamfer restatement, "
-                      "AVX2, %d threads), linearly extrapolated, retries not added"
-                      % (KERNEL, n_it, ITERS, sec, cores)}
+            "kind": "port", "sample": cpu_sample_text(n_it, sec, cores)}
     sys.stdout.flush()
     os.dup2(real_stdout, 1)
     print(json.dumps(line))
