@@ -475,21 +475,15 @@ extern "C" int houv_pose_optimise_ex(const HouvPoseProblem *q, void *stream) {
             return a.wview == 0.f ? launch_pose_sym(a, 84, st) : launch_pose_duo(a, false, st);
         case 21:  // the same with the column reduction pipelined under the sweep
             return a.wview == 0.f ? launch_pose_sym(a, 84, st) : launch_pose_duo(a, true, st);
-        case 10: return launch_pose_sym(a, 2, st);
-        case 11: return launch_pose_sym(a, 4, st);
-        case 12: return launch_pose_sym(a, 8, st);
-        case 13: return launch_pose_sym(a, 84, st);
-        case 14: return launch_pose_sym(a, 44, st);
+        case 12: return launch_pose_sym(a, 8, st);     // one row per CTA, two rows evaluated before their folds
+        case 13: return launch_pose_sym(a, 84, st);    // one row per CTA, four rows before their folds (round-1 default)
         case 15: return launch_pose_sym(a, 1004, st);  // four-metric sweep even when wview == 0
         case 16: return launch_pose_sym(a, 1008, st);  // variant 12 with the (distance, index) recovery
         case 17: return launch_pose_sym(a, 1009, st);  // ... with it only where no minimum is stored
-        case 1: return launch_pose<4, 1, 2>(a, st);
-        case 2: return launch_pose<4, 2, 1>(a, st);
-        case 3: return launch_pose<2, 1, 2>(a, st);
-        case 4: return launch_pose<2, 2, 2>(a, st);
-        case 5: return launch_pose<4, 2, 2>(a, st);
-        case 0:
-        default: return launch_pose<4, 1, 1>(a, st);
+        case 0: return launch_pose<4, 1, 1>(a, st);    // two directed scans
+        // the other unroll / query-blocking variants measured in round 1 (1-5, 10, 11, 14:
+        // profiles/r1_ncu_summary.md) lost and were pruned from the build
+        default: return HOUV_E_BADARG;
     }
 }
 

@@ -556,11 +556,9 @@ int launch_pose_sym(const PoseArgs &a, int unroll, cudaStream_t st) {
     if (a.wview == 0.f && unroll != 1004)
         return unroll == 84 ? launch_sym<8, 4, 1>(a, st) : launch_sym<8, 2, 1>(a, st);
     switch (unroll) {
-        case 4: return launch_sym<4, 2, 4>(a, st);
         case 8: case 1004: return launch_sym<8, 2, 4>(a, st);
         case 84: return launch_sym<8, 4, 4>(a, st);
-        case 44: return launch_sym<4, 4, 4>(a, st);
-        default: return launch_sym<2, 2, 4>(a, st);
+        default: return HOUV_E_BADARG;  // (unrolls 2 / 4 of round 1 were pruned)
     }
 }
 

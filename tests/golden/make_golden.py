@@ -159,6 +159,44 @@ def make_solve():
     print("solve fixtures written")
 
 
+def make_solve_full():
+    """solve_full.npz: the reference's OWN train_utils.getPredict_angle (train_utils.py:359-452,
+    unmodified) at the shape test.py:64 runs it -- 2048 points x 64 starts x 500 Adam iterations at
+    lr 0.1, float64 leaves -- on two well-conditioned pairs (synth.make_overlap_pair), NumPy seeded
+    just before the call.  min_1 of every forward is recorded by wrapping (not editing) the module's
+    calc_cd_percent name; metrics.cd as in make_houv_full."""
+    import time
+    import torch
+    import ref_loader
+    from houv_b200 import synth
+    from oracle import chamfer as oc
+    oc.set_threads(os.cpu_count() or 8)
+    ref_loader.FAST_CD = True
+    tu = ref_loader.load()["tu"]
+    pairs = [synth.make_overlap_pair(10 + i) for i in range(2)]
+    s, t, tr = (np.stack([q[k] for q in pairs]) for k in range(3))
+    src, tgt = torch.from_numpy(s), torch.from_numpy(t)
+    trace = []
+    orig = tu.calc_cd_percent
+
+    def rec(a, b, *k, **kw):
+        cd_t, cd_p = orig(a, b, *k, **kw)
+        trace.append(torch.min(cd_t, cd_p).detach().numpy().copy())
+        return cd_t, cd_p
+    tu.calc_cd_percent = rec
+    try:
+        np.random.seed(91)
+        t0 = time.time()
+        l, R, T, ts = tu.getPredict_angle(src, tgt, kernel=64, num_epochs=500, angle_base=0)
+        print("getPredict_angle 2 pairs x 64 x 500: %.0f s" % (time.time() - t0), flush=True)
+    finally:
+        tu.calc_cd_percent = orig
+    np.savez_compressed(os.path.join(HERE, "solve_full.npz"), src=s, tgt=t, transform=tr, seed=np.int32(91),
+                        trace=np.stack(trace).astype(np.float32), min_1=l.detach().numpy(),
+                        R=R.detach().numpy(), T=T.detach().numpy(), tran_s=ts.detach().numpy())
+    print("solve_full written", np.stack(trace).shape, l.detach().numpy().min(1))
+
+
 def make_calccd():
     """calccd_ref.npz: the reference's own calc_cd (model_utils_completion.py:69-80, identical to
     completion/model_utils.py:69-80) with calc_f1, and the gradient of mean(cd_p)+mean(cd_t) with
@@ -343,7 +381,7 @@ def make_houv_full(n_easy=2, hard=(3,), tag="houv_full", reversed_atomics=False)
     print(tag, "written: r_err", out["r_err"], "t_err", out["t_err"], "calls", len(calls))
 
 
-FAMILIES = {"small": make_small, "houv_full": make_houv_full,
+FAMILIES = {"small": make_small, "solve_full": make_solve_full, "houv_full": make_houv_full,
             # the same run with the reference kernel's gradient adds in the opposite order: the
             # reference against ITSELF (ref_loader.BACKWARD_REVERSED)
             "houv_full_alt": lambda: make_houv_full(tag="houv_full_alt", reversed_atomics=True),
