@@ -341,6 +341,239 @@ __global__ void __launch_bounds__(kGThreads, 2) grad_gather_kernel(const GradArg
     }
 }
 
+// ---------------------------------------------------------------------------------------------
+// The deterministic gather kernel, PIPELINED (round 2): one persistent CTA of 1024 threads per SM.
+// A batch element's six arrays (xyz1, xyz2, graddist1, graddist2, idx1, idx2: 80 KB at 2048 points)
+// are contiguous in global memory: ONE thread brings the next element in with six TMA bulk copies
+// (cp.async.bulk + mbarrier, two buffers) while all threads invert / gather the current one, and
+// the finished gradient rows leave from shared memory by bulk store (assign) or bulk reduce-add
+// (accumulate: one float add per address, still deterministic).  Global traffic is in flight all
+// the time instead of between the phases of one element.  Same summation order, same bits as
+// grad_gather_kernel.  Needs N, M multiples of 4 (16-byte rows) and 16-byte aligned arrays; other
+// shapes take grad_gather_kernel.
+constexpr int kG2Threads = 1024;
+
+struct Gather2Stage {
+    float s1[kGMax * 3], s2[kGMax * 3];  // clouds in; gradient rows out (same place)
+    float gd1[kGMax], gd2[kGMax];
+    int ix1[kGMax], ix2[kGMax];
+};
+struct Gather2Smem {
+    Gather2Stage st[2];
+    unsigned short start1[kGMax + 2], start2[kGMax + 2];
+    unsigned short list1[kGMax], list2[kGMax];
+    int cnt1[kGMax], cnt2[kGMax];
+    int wsum[2][kG2Threads / 32];
+    unsigned long long full[2];
+};
+
+__device__ __forceinline__ unsigned g2_u32(const void *p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void g2_load(void *dst, const void *src, unsigned bytes, unsigned long long *bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::
+                     "r"(g2_u32(dst)), "l"(src), "r"(bytes), "r"(g2_u32(bar))
+                 : "memory");
+}
+__device__ __forceinline__ void g2_store(void *dst, const void *src, unsigned bytes, bool add) {
+    if (add)
+        asm volatile("cp.reduce.async.bulk.global.shared::cta.bulk_group.add.f32 [%0], [%1], %2;" ::"l"(dst),
+                     "r"(g2_u32(src)), "r"(bytes)
+                     : "memory");
+    else
+        asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(g2_u32(src)),
+                     "r"(bytes)
+                     : "memory");
+}
+__device__ __forceinline__ void g2_wait(unsigned long long *bar, unsigned parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONE_%=;\n"
+        "bra WAIT_%=;\n"
+        "DONE_%=:\n"
+        "}\n" ::"r"(g2_u32(bar)),
+        "r"(parity)
+        : "memory");
+}
+
+// the scattered terms of bucket [p0, p0+L), ascending point index (as gather_bucket, int indices).
+// Buckets of up to 4 entries (nearly all: a point is the nearest neighbour of one other point on
+// average): entries loaded together, sorted in registers by a 5-exchange network, their data loaded
+// independently, then added in order -- no LDS -> LDS -> FADD chain per entry.
+__device__ __forceinline__ void g2_bucket(unsigned short *list, int p0, int L, const int *ix, int n_src, int k,
+                                          const float *sa, const float *gd, float bx, float by, float bz,
+                                          float (&acc)[3]) {
+    auto add = [&](int i) {
+        const float g = __fmul_rn(gd[i], 2.f);
+        acc[0] = __fadd_rn(acc[0], -__fmul_rn(g, __fsub_rn(sa[3 * i + 0], bx)));
+        acc[1] = __fadd_rn(acc[1], -__fmul_rn(g, __fsub_rn(sa[3 * i + 1], by)));
+        acc[2] = __fadd_rn(acc[2], -__fmul_rn(g, __fsub_rn(sa[3 * i + 2], bz)));
+    };
+    if (L == 0) return;
+    if (L <= 4) {
+        unsigned e[4];
+#pragma unroll
+        for (int a = 0; a < 4; ++a) e[a] = a < L ? (unsigned)list[p0 + a] : 0xffffu;  // sentinels sort last
+        auto cswap = [](unsigned &x, unsigned &y) { const unsigned lo = min(x, y), hi = max(x, y); x = lo; y = hi; };
+        cswap(e[0], e[1]); cswap(e[2], e[3]); cswap(e[0], e[2]); cswap(e[1], e[3]); cswap(e[1], e[2]);
+        float t0[4], t1[4], t2[4];
+#pragma unroll
+        for (int a = 0; a < 4; ++a) {
+            const int i = a < L ? (int)e[a] : 0;
+            const float g = __fmul_rn(gd[i], 2.f);
+            t0[a] = -__fmul_rn(g, __fsub_rn(sa[3 * i + 0], bx));
+            t1[a] = -__fmul_rn(g, __fsub_rn(sa[3 * i + 1], by));
+            t2[a] = -__fmul_rn(g, __fsub_rn(sa[3 * i + 2], bz));
+        }
+#pragma unroll
+        for (int a = 0; a < 4; ++a) {
+            if (a < L) {
+                acc[0] = __fadd_rn(acc[0], t0[a]); acc[1] = __fadd_rn(acc[1], t1[a]); acc[2] = __fadd_rn(acc[2], t2[a]);
+            }
+        }
+        return;
+    }
+    if (L <= kGSortMax) {
+        for (int a = 1; a < L; ++a) {
+            const unsigned short v = list[p0 + a];
+            int b = a - 1;
+            while (b >= 0 && list[p0 + b] > v) { list[p0 + b + 1] = list[p0 + b]; --b; }
+            list[p0 + b + 1] = v;
+        }
+        for (int a = 0; a < L; ++a) add(list[p0 + a]);
+    } else {
+        for (int i = 0; i < n_src; ++i)
+            if (ix[i] == k) add(i);
+    }
+}
+
+// exclusive scans of cnt1[0..m) -> start1[0..m] and cnt2[0..n) -> start2[0..n]; both cnt arrays reset to 0
+__device__ __forceinline__ void g2_scan2(Gather2Smem &S, int n, int m) {
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    const int a0 = 2 * t < m ? S.cnt1[2 * t] : 0, a1 = 2 * t + 1 < m ? S.cnt1[2 * t + 1] : 0;
+    const int b0 = 2 * t < n ? S.cnt2[2 * t] : 0, b1 = 2 * t + 1 < n ? S.cnt2[2 * t + 1] : 0;
+    const int sa = a0 + a1, sb = b0 + b1;
+    int ia = sa, ib = sb;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int va = __shfl_up_sync(0xffffffffu, ia, o), vb = __shfl_up_sync(0xffffffffu, ib, o);
+        if (lane >= o) { ia += va; ib += vb; }
+    }
+    if (lane == 31) { S.wsum[0][warp] = ia; S.wsum[1][warp] = ib; }
+    __syncthreads();
+    const int wa = S.wsum[0][lane], wb = S.wsum[1][lane];  // 32 warps: one per lane
+    int ja = wa, jb = wb;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int va = __shfl_up_sync(0xffffffffu, ja, o), vb = __shfl_up_sync(0xffffffffu, jb, o);
+        if (lane >= o) { ja += va; jb += vb; }
+    }
+    const int offa = __shfl_sync(0xffffffffu, ja - wa, warp), offb = __shfl_sync(0xffffffffu, jb - wb, warp);
+    const int tota = __shfl_sync(0xffffffffu, ja, 31), totb = __shfl_sync(0xffffffffu, jb, 31);
+    const int ra = offa + ia - sa, rb = offb + ib - sb;
+    if (2 * t < m) { S.start1[2 * t] = (unsigned short)ra; S.cnt1[2 * t] = 0; }
+    if (2 * t + 1 < m) { S.start1[2 * t + 1] = (unsigned short)(ra + a0); S.cnt1[2 * t + 1] = 0; }
+    if (2 * t < n) { S.start2[2 * t] = (unsigned short)rb; S.cnt2[2 * t] = 0; }
+    if (2 * t + 1 < n) { S.start2[2 * t + 1] = (unsigned short)(rb + b0); S.cnt2[2 * t + 1] = 0; }
+    if (t == 0) { S.start1[m] = (unsigned short)tota; S.start2[n] = (unsigned short)totb; }
+}
+
+__global__ void __launch_bounds__(kG2Threads, 1) grad_gather2_kernel(const GradArgs args, int B, bool assign) {
+    extern __shared__ __align__(128) unsigned char g2_raw[];
+    Gather2Smem &S = *reinterpret_cast<Gather2Smem *>(g2_raw);
+    const int n = args.dir[0].n, m = args.dir[0].m, t = threadIdx.x;
+    const unsigned bytes = (unsigned)(n + m) * 20u;  // 12 xyz + 4 graddist + 4 idx per point
+    if (t == 0) {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(g2_u32(&S.full[0])));
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(g2_u32(&S.full[1])));
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    for (int i = t; i < kGMax; i += kG2Threads) { S.cnt1[i] = 0; S.cnt2[i] = 0; }
+    __syncthreads();
+    auto issue = [&](int b, int p) {  // thread 0: the six arrays of element b into buffer p
+        Gather2Stage &T = S.st[p];
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(g2_u32(&S.full[p])), "r"(bytes)
+                     : "memory");
+        g2_load(T.s1, args.dir[0].a + (size_t)b * n * 3, (unsigned)n * 12u, &S.full[p]);
+        g2_load(T.s2, args.dir[0].b + (size_t)b * m * 3, (unsigned)m * 12u, &S.full[p]);
+        g2_load(T.gd1, args.dir[0].gd + (size_t)b * n, (unsigned)n * 4u, &S.full[p]);
+        g2_load(T.gd2, args.dir[1].gd + (size_t)b * m, (unsigned)m * 4u, &S.full[p]);
+        g2_load(T.ix1, args.dir[0].idx + (size_t)b * n, (unsigned)n * 4u, &S.full[p]);
+        g2_load(T.ix2, args.dir[1].idx + (size_t)b * m, (unsigned)m * 4u, &S.full[p]);
+    };
+    if (t == 0 && (int)blockIdx.x < B) issue(blockIdx.x, 0);
+    int k = 0;
+    for (int b = blockIdx.x; b < B; b += gridDim.x, ++k) {
+        const int p = k & 1;
+        Gather2Stage &T = S.st[p];
+        if (t == 0 && b + (int)gridDim.x < B) {
+            // buffer p^1 still feeds the bulk stores of the previous element: wait until they have READ it
+            asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            issue(b + gridDim.x, p ^ 1);
+        }
+        g2_wait(&S.full[p], (unsigned)(k >> 1) & 1u);
+        // bucket sizes: direction 1 scatters into the m points of cloud 2, direction 2 into cloud 1
+        for (int i = t; i < n; i += kG2Threads) atomicAdd(&S.cnt1[T.ix1[i]], 1);
+        for (int j = t; j < m; j += kG2Threads) atomicAdd(&S.cnt2[T.ix2[j]], 1);
+        __syncthreads();
+        g2_scan2(S, n, m);
+        __syncthreads();
+        for (int i = t; i < n; i += kG2Threads) {
+            const int kk = T.ix1[i];
+            S.list1[S.start1[kk] + atomicAdd(&S.cnt1[kk], 1)] = (unsigned short)i;
+        }
+        for (int j = t; j < m; j += kG2Threads) {
+            const int kk = T.ix2[j];
+            S.list2[S.start2[kk] + atomicAdd(&S.cnt2[kk], 1)] = (unsigned short)j;
+        }
+        __syncthreads();
+        float r1[2][3], r2[2][3];
+#pragma unroll
+        for (int q = 0; q < 2; ++q) {
+            const int i = t + q * kG2Threads;
+            if (i < n) {  // row of cloud 1: own term of direction 1, then what direction 2 scatters
+                const float ax = T.s1[3 * i], ay = T.s1[3 * i + 1], az = T.s1[3 * i + 2];
+                const int j = T.ix1[i];
+                const float g = __fmul_rn(T.gd1[i], 2.f);
+                r1[q][0] = __fadd_rn(0.f, __fmul_rn(g, __fsub_rn(ax, T.s2[3 * j + 0])));
+                r1[q][1] = __fadd_rn(0.f, __fmul_rn(g, __fsub_rn(ay, T.s2[3 * j + 1])));
+                r1[q][2] = __fadd_rn(0.f, __fmul_rn(g, __fsub_rn(az, T.s2[3 * j + 2])));
+                g2_bucket(S.list2, S.start2[i], S.cnt2[i], T.ix2, m, i, T.s2, T.gd2, ax, ay, az, r1[q]);
+                S.cnt2[i] = 0;  // ready for the next element's count
+            }
+            const int kk = t + q * kG2Threads;
+            if (kk < m) {  // row of cloud 2: what direction 1 scatters, then the own term of direction 2
+                const float bx = T.s2[3 * kk], by = T.s2[3 * kk + 1], bz = T.s2[3 * kk + 2];
+                r2[q][0] = 0.f; r2[q][1] = 0.f; r2[q][2] = 0.f;
+                g2_bucket(S.list1, S.start1[kk], S.cnt1[kk], T.ix1, n, kk, T.s1, T.gd1, bx, by, bz, r2[q]);
+                S.cnt1[kk] = 0;
+                const int i2 = T.ix2[kk];
+                const float g = __fmul_rn(T.gd2[kk], 2.f);
+                r2[q][0] = __fadd_rn(r2[q][0], __fmul_rn(g, __fsub_rn(bx, T.s1[3 * i2 + 0])));
+                r2[q][1] = __fadd_rn(r2[q][1], __fmul_rn(g, __fsub_rn(by, T.s1[3 * i2 + 1])));
+                r2[q][2] = __fadd_rn(r2[q][2], __fmul_rn(g, __fsub_rn(bz, T.s1[3 * i2 + 2])));
+            }
+        }
+        __syncthreads();  // everybody is done reading the clouds: the gradient rows take their place
+#pragma unroll
+        for (int q = 0; q < 2; ++q) {
+            const int i = t + q * kG2Threads;
+            if (i < n) { T.s1[3 * i] = r1[q][0]; T.s1[3 * i + 1] = r1[q][1]; T.s1[3 * i + 2] = r1[q][2]; }
+            if (i < m) { T.s2[3 * i] = r2[q][0]; T.s2[3 * i + 1] = r2[q][1]; T.s2[3 * i + 2] = r2[q][2]; }
+        }
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        __syncthreads();
+        if (t == 0) {
+            g2_store(args.dir[0].ga + (size_t)b * n * 3, T.s1, (unsigned)n * 12u, !assign);
+            g2_store(args.dir[0].gb + (size_t)b * m * 3, T.s2, (unsigned)m * 12u, !assign);
+            asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+        }
+    }
+    if (t == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+}
+
 }  // namespace houv
 
 using namespace houv;
@@ -376,10 +609,25 @@ static int backward_impl(const float *xyz1, const float *xyz2, const float *grad
                                                   (((size_t)M * 3 + 3) & ~(size_t)3));
     const bool fits = res_bytes <= 200 * 1024;
     // The deterministic gather kernel (clouds up to 2048 points) on request -- the _deterministic
-    // entry point or HOUV_K2_VARIANT=2; it costs ~1.5x the float-atomics kernels (measured, B200:
-    // 6400 x 2048^2 447 us against 290 us resident; 32 x 2048^2 20.5 us against 13.3 us streaming).
+    // entry point or HOUV_K2_VARIANT=2 / 3; it costs ~1.4x the float-atomics kernels (measured, B200:
+    // 6400 x 2048^2 448 us, pipelined 407 us, against 290 us resident; 32 x 2048^2 16.4 us against 14 us).
     // HOUV_K2_VARIANT: 1 = the float-atomics resident kernel, 0 = streaming.
     if (deterministic && (N > kGMax || M > kGMax)) return HOUV_E_TOOBIG;
+    // 3 (and the deterministic entry point when the layout allows): the same sums, TMA-pipelined
+    const bool al16 = ((reinterpret_cast<uintptr_t>(xyz1) | reinterpret_cast<uintptr_t>(xyz2) |
+                        reinterpret_cast<uintptr_t>(graddist1) | reinterpret_cast<uintptr_t>(graddist2) |
+                        reinterpret_cast<uintptr_t>(idx1) | reinterpret_cast<uintptr_t>(idx2) |
+                        reinterpret_cast<uintptr_t>(gradxyz1) | reinterpret_cast<uintptr_t>(gradxyz2)) & 15) == 0;
+    const bool can_pipe = N <= kGMax && M <= kGMax && N % 4 == 0 && M % 4 == 0 && al16;
+    if (can_pipe && (forced == 3 || (forced < 0 && deterministic))) {
+        int dev = 0, sms = 148;
+        if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        const int grid = B < sms ? B : sms;
+        static unsigned long long g2smem_set = 0;
+        if (int e = ensure_dyn_smem(grad_gather2_kernel, (int)sizeof(Gather2Smem), g2smem_set)) return e;
+        grad_gather2_kernel<<<grid, kG2Threads, sizeof(Gather2Smem), (cudaStream_t)stream>>>(a, B, assign);
+        return check_launch();
+    }
     if (N <= kGMax && M <= kGMax && (forced == 2 || (forced < 0 && deterministic))) {
         int grid = 2 * 148;
         if (grid > B) grid = B;

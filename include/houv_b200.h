@@ -115,7 +115,8 @@ int houv_chamfer3d_backward_assign(const float *xyz1, const float *xyz2, const f
  * the result is identical run to run and bit-identical to the reference kernel bodies executed
  * sequentially (oracle/chamfer_oracle.c) -- the reference's float atomics are order-dependent
  * (chamfer3D.cu:166-171, registration/README.md:82-90).  assign != 0 writes the buffers, 0 adds
- * into them.  Clouds up to 2048 points (HOUV_E_TOOBIG above); ~1.5x the time of the default.
+ * into them.  Clouds up to 2048 points (HOUV_E_TOOBIG above); ~1.4x the time of the default
+ * (TMA-pipelined when the arrays are 16-byte aligned and N, M are multiples of 4).
  * The Python layer calls this under torch.use_deterministic_algorithms(True). */
 int houv_chamfer3d_backward_deterministic(const float *xyz1, const float *xyz2,
                                           const float *graddist1, const float *graddist2,

@@ -168,7 +168,8 @@ def test_autograd_backward_vs_float64_oracle(shape):
     assert _grad_close(t1.grad.cpu().numpy(), h1) and _grad_close(t2.grad.cpu().numpy(), h2)
 
 
-@pytest.mark.parametrize("k2", ["0", "1", "2"], ids=["k2-streaming", "k2-resident", "k2-gather"])
+@pytest.mark.parametrize("k2", ["0", "1", "2", "3"],
+                         ids=["k2-streaming", "k2-resident", "k2-gather", "k2-gather-pipelined"])
 @pytest.mark.parametrize("shape", [(3, 7, 13), (5, 1001, 999), (2, 1, 1), (150, 2048, 2048),
                                    (3, 3000, 5500)])
 def test_backward_both_kernels_vs_float64_oracle(shape, k2, monkeypatch):
@@ -259,7 +260,8 @@ def test_extreme_finite_inputs(n, m):
     _check_fwd(x2, x1)
 
 
-@pytest.mark.parametrize("shape", [(3, 7, 13), (5, 1001, 999), (2, 1, 1), (40, 2048, 2048), (4, 2048, 300)])
+@pytest.mark.parametrize("shape", [(3, 7, 13), (5, 1001, 999), (2, 1, 1), (40, 2048, 2048), (4, 2048, 300),
+                                   (700, 512, 1024), (149, 2048, 2048), (3, 4, 8)])
 def test_backward_is_deterministic_and_bit_exact(shape):
     """Under torch.use_deterministic_algorithms(True) clouds up to 2048 points take the gather-side
     kernel (houv_chamfer3d_backward_deterministic): every gradient row is summed by one thread in
