@@ -194,6 +194,27 @@ def _pose_optimise_large(src, tgt, params, kernel, iters, angle_base, grad_scale
     return dict(min_1=min1, R=R_out, T=T_out, loss=loss_out, trace=trace, tran_s=ts_out)
 
 
+def _k3_kernel_launches(rows, kernel, has_row_pair, wview, dev):
+    """Kernels one houv_pose_optimise_ex call launches (for bench.py's gpu_launches): mirrors
+    csrc/pose_duo.cu launch_duo for the default variant -- whole waves of two-row CTAs, the rows that
+    cannot be paired (caller-made row_pair, odd K) through the one-row kernel, and a one-row tail when
+    what is left fits one wave.  Other variants (HOUV_POSE_VARIANT, a loss without view terms) launch one."""
+    import os
+    if wview == 0.0 or os.environ.get("HOUV_POSE_VARIANT", "20") not in ("20", "21") or rows == 0:
+        return 1 if rows else 0
+    sms = torch.cuda.get_device_properties(dev).multi_processor_count
+    nduo = rows // 2
+    whole = nduo // sms * sms
+    if whole > 0 and rows - 2 * whole <= sms:
+        nduo = whole
+    n = 0
+    if nduo > 0:
+        n += 1 + (1 if (has_row_pair or kernel % 2) else 0)
+    if rows > 2 * nduo:
+        n += 1
+    return n
+
+
 def pose_optimise(src, tgt, params, kernel, iters, angle_base=0, grad_scale=None,
                   adam_m=None, adam_v=None, step0=0, lr=ADAM_LR, betas=ADAM_BETAS, eps=ADAM_EPS,
                   percent=ALPHA, w3d=W_3D, wview=W_VIEW, want_loss=False, want_trace=False,
@@ -278,7 +299,7 @@ def pose_optimise(src, tgt, params, kernel, iters, angle_base=0, grad_scale=None
     with torch.cuda.device(dev):
         rc = _lib.load().houv_pose_optimise_ex(ctypes.byref(q), _lib.stream_ptr())
     _lib.check(rc, "houv_pose_optimise_ex")
-    _lib.count_launches(1)
+    _lib.count_launches(_k3_kernel_launches(rows, kernel, row_pair is not None, wview, dev))
     if timing is not None:
         ev1.record()
         timing.append((ev0, ev1, rows, iters, N))
