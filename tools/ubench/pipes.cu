@@ -6,6 +6,20 @@
 
 #define MIN3(d, a, b, c) asm volatile("min.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c))
 #define MIN2(d, a, b) asm volatile("min.f32 %0, %1, %2;" : "=f"(d) : "f"(a), "f"(b))
+// integer 3-input minimum on the float bit patterns (DPX; __vimin3_s32 -> VIMNMX3): non-negative floats order
+// like signed integers, so for squared distances it folds the same values as FMNMX3
+#define IMIN3(d, a, b, c)                                                                               \
+    do {                                                                                                \
+        int r_ = __vimin3_s32(__float_as_int(a), __float_as_int(b), __float_as_int(c));                 \
+        asm volatile("" : "+r"(r_));                                                                    \
+        d = __int_as_float(r_);                                                                         \
+    } while (0)
+#define UMIN3(d, a, b, c)                                                                               \
+    do {                                                                                                \
+        unsigned r_ = __vimin3_u32(__float_as_uint(a), __float_as_uint(b), __float_as_uint(c));         \
+        asm volatile("" : "+r"(r_));                                                                    \
+        d = __uint_as_float(r_);                                                                        \
+    } while (0)
 #define FMA2(d, a, b, c)                                                              \
     asm volatile("fma.rn.f32x2 %0, %1, %2, %3;"                                       \
                  : "=l"(d)                                                            \
@@ -55,6 +69,18 @@ __global__ void __launch_bounds__(512, 1) k(float *out, long long *cyc, int iter
                     FMA2(p[i], p[i], q[i], q[i]);
                     asm volatile("add.s32 %0, %0, %1;" : "+r"(*(int*)&x[i]) : "r"(*(int*)&y[i]));
                 }
+                if (MODE == 13) { IMIN3(m[i], m[i], x[i], y[i]); }
+                if (MODE == 14) { FMA2(p[i], p[i], q[i], q[i]); IMIN3(m[i], m[i], x[i], y[i]); }
+                if (MODE == 15) {  // 9 packed : 8 integer min3
+                    FMA2(p[i], p[i], q[i], q[i]); IMIN3(m[i], m[i], x[i], y[i]);
+                    if (i == 0) FMA2(p[1], p[1], q[0], q[0]);
+                }
+                if (MODE == 16) { UMIN3(m[i], m[i], x[i], y[i]); }
+                if (MODE == 17) {  // 2-input integer min
+                    int r_ = min(__float_as_int(m[i]), __float_as_int(x[i]));
+                    asm volatile("" : "+r"(r_));
+                    m[i] = __int_as_float(r_);
+                }
                 if (MODE == 7) {  // min3 on operands produced by the FMA pipe (cross-pipe forwarding)
                     FMA2(p[i], p[i], q[i], q[i]);
                     float lo = __uint_as_float((unsigned)p[i]), hi = __uint_as_float((unsigned)(p[i] >> 32));
@@ -101,6 +127,11 @@ int main() {
         run<10>("FFMA2 + 2xFMNMX", 12 * NCH, th);
         run<11>("FADD2 bcast + FMNMX3", 8 * NCH, th);
         run<12>("FFMA2 + IADD", 8 * NCH, th);
+        run<13>("VIMNMX3 (s32)", 4 * NCH, th);
+        run<16>("VIMNMX3 (u32)", 4 * NCH, th);
+        run<17>("IMNMX 2-input (s32)", 4 * NCH, th);
+        run<14>("FFMA2+VIMNMX3 1:1", 8 * NCH, th);
+        run<15>("FFMA2:VIMNMX3 9:8", 4 * (2 * NCH + 1), th);
     }
     return 0;
 }
