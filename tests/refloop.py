@@ -52,3 +52,27 @@ def reference_predict_model(src, tgt, kernel=64, num_epochs=200, angle_base=0):
         L.cd = old
     return (min_1.detach().reshape(B, kernel), R.detach().reshape(B, kernel, 3, 3),
             T.detach().reshape(B, kernel, 3))
+
+
+def reference_solve_model(src, tgt, kernel=64, num_epochs=200, threshold=0.030):
+    """solve_model (houv.py:142-206) over reference_predict_model: angle_base 0 for every pair, then
+    angle_base 1..3 on the sub-batch whose best start stays above 0.030, kept where better.
+    -> ans[B,4,4] (zero bottom row), retried[B] bool."""
+    B = src.shape[0]
+    rmse_loss, R, T = reference_predict_model(src, tgt, kernel, num_epochs, 0)
+    rmse = rmse_loss.min(dim=1).values
+    lst = torch.nonzero(rmse > threshold).reshape(-1)
+    retried = torch.zeros(B, dtype=torch.bool, device=src.device)
+    retried[lst] = True
+    if lst.numel() > 0:
+        for base in (1, 2, 3):
+            l_add, R_add, T_add = reference_predict_model(src[lst], tgt[lst], kernel, num_epochs, base)
+            r_add = l_add.min(dim=1).values
+            flag = torch.nonzero(r_add < rmse[lst]).reshape(-1)
+            geid = lst[flag]
+            R[geid], rmse_loss[geid], T[geid], rmse[geid] = R_add[flag], l_add[flag], T_add[flag], r_add[flag]
+    best = rmse_loss.argmin(dim=1)
+    idx = torch.arange(B, device=src.device)
+    ans = torch.zeros(B, 4, 4, device=src.device)
+    ans[:, :3, :3], ans[:, :3, 3] = R[idx, best], T[idx, best]
+    return ans, retried
