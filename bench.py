@@ -25,7 +25,8 @@ collective).  Weak scaling: every rank holds --pairs-per-gpu pairs (150 = the
 `extra`      the same step on the HARD set (objects twice the size: ~20 % of the pairs go
              through the retry cascade, like MVP's unrestricted rotations), K1/K2 at
              BASELINE configs 2 and 5 beside the reference's own CUDA extension, K2 against
-             the measured HBM peak, the ICP baseline (config 3), and -- once, untimed --
+             the measured HBM peak, the ICP baseline (config 3), a bounded sample of the reference's
+             own GPU loop over its unmodified extension (8 pairs), and -- once, untimed --
              `parity_checked` against the reference-made full-size fixture.
 `cpu_baseline` / --impl reference: the CPU oracle of the same path (restated
              houv.py over the multi-threaded C chamfer oracle) on the box's host
@@ -309,6 +310,37 @@ def icp_line(dev, flush):
             "parity": "unpinned (Open3D 0.9.0 unavailable on this box)"}
 
 
+def reference_gpu_loop_line(dev, d_src, d_tgt, pairs=8):
+    """A bounded sample of the reference's OWN loop on this GPU, beside ours: predict_model as the
+    reference runs it (torch HOUV.forward, Predict_loss = 4 chamfer calls + 8 top-k, autograd, torch
+    Adam; houv.py:106-138) over the reference's unmodified CUDA extension built for sm_100a
+    (oracle/_ref/chamfer_3D.so through tests/refloop.py -- an extra leg like cpu_baseline, never on
+    the product path), `pairs` pairs x 64 starts x 200 iterations at angle_base 0, buffers allocated
+    on the device (kinder than the reference wrapper's CPU-side zeros)."""
+    import torch
+    from oracle import ref_ext
+    if not ref_ext.available():
+        return {"unavailable": "oracle/_ref/chamfer_3D.so was not built"}
+    from houv_b200 import solver
+    from tests.refloop import reference_predict_model
+    a, b = d_src[:pairs].contiguous(), d_tgt[:pairs].contiguous()
+    out = {}
+    for name, fn in (("reference_loop", lambda: reference_predict_model(a, b, num_epochs=ITERS)),
+                     ("fused", lambda: solver.predict_model(solver.HOUV(pairs * KERNEL, 0), a, b, kernel=KERNEL,
+                                                            num_epochs=ITERS))):
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        m, _, _ = fn()
+        torch.cuda.synchronize()
+        out[name] = (time.perf_counter() - t0, m.min(dim=1).values)
+    rel = ((out["fused"][1] - out["reference_loop"][1]).abs() / out["reference_loop"][1]).median()
+    return {"workload": "%d pairs x %d starts x %d its at angle_base 0, first pass only" % (pairs, KERNEL, ITERS),
+            "reference_loop_pairs_per_s": pairs / out["reference_loop"][0],
+            "fused_pairs_per_s_same_call": pairs / out["fused"][0],
+            "note": "the fused call holds 512 rows = 1.7 waves, so it runs below the step's rate",
+            "best_min_1_rel_diff_median": float(rel)}
+
+
 def parity_summary():
     """Once, outside every timed region: K3 / solve_model at the full BASELINE shape against the
     fixture made by the reference's own solve_model (houv_b200/parity.py)."""
@@ -581,6 +613,10 @@ def run_ours(args):
     # second half of BASELINE.json's metric: Chamfer NN throughput of the operator on its own
     # (K1; chamfer_3DDist forward, both directions), directed point pairs per second
     line["chamfer_nn"] = chamfer_operator_lines(dev, flush, fp32_peak)
+    try:
+        line["extra"]["reference_gpu_loop"] = reference_gpu_loop_line(dev, d_src, d_tgt)
+    except Exception as e:
+        line["extra"]["reference_gpu_loop"] = {"error": repr(e)}
     try:
         line["extra"]["icp_c3"] = icp_line(dev, flush)
     except Exception as e:
