@@ -266,7 +266,11 @@ def chamfer_operator_lines(dev, flush, fp32_peak):
         pairs = 2.0 * B * N * M
         k2_bytes = 32.0 * B * (N + M)
         e = {"ms": ms, "Gpts2_per_s": pairs / ms / 1e6,
+             # 16*B*N*M algorithmic FLOP per forward (8 per DIRECTED pair).  The symmetric
+             # kernel (all three shapes take it) evaluates every d(i,j) once for both directions, so it
+             # executes half of that: 6 FMA-pipe + 2 ALU-pipe lane-cycles per undirected pair.
              "frac_fp32_peak": 8.0 * pairs / ms / 1e9 / fp32_peak,
+             "executed_frac_fp32_peak": 4.0 * pairs / ms / 1e9 / fp32_peak,
              "fwd_bwd_ms": ms_fb,
              "k2_backward": {"ms": ms_b, "algorithmic_bytes": k2_bytes,
                              "achieved_GBps": k2_bytes / ms_b / 1e6, "peak_GBps": hbm,
